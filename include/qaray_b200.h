@@ -1,0 +1,227 @@
+/* qaray_b200.h — C ABI of the B200 renderer for qaray's per-pixel Monte-Carlo loop.
+ *
+ * The reference (wilsonCernWq/qaray) has no FFI: its plug-in seam is the C++ `Renderer` subclass contract
+ *     r->Init(); LoadScene(file); r->ComputeScene(renderImage, scene); r->Render(); r->Terminate();
+ * (src/main.cpp:55-59, src/renderers/renderer.h:101-110), with `Renderer::ThreadRender` -> `PixelRender`
+ * (src/renderers/renderer.cpp:302-423) as the hot path. This header is what a binding for that seam talks to:
+ * plain pointers and sizes, one opaque scene handle, no C++ or torch types. Every entry point names the
+ * reference interface it replaces. All functions return 0 on success or a negative QG_E* code; the message is
+ * available from qg_last_error() (thread-local). The library copies every host buffer it is given.
+ *
+ * There is no CPU fallback: every compute entry point fails with QG_ENODEVICE when no CUDA device is usable.
+ */
+#ifndef QARAY_B200_H
+#define QARAY_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define QG_OK 0
+#define QG_EINVAL (-1)   /* bad argument */
+#define QG_EIO (-2)      /* scene / asset file could not be read (LoadScene returning 0, xmlload.cpp:71-95) */
+#define QG_ENODEVICE (-3) /* no usable CUDA device */
+#define QG_ECUDA (-4)    /* a CUDA call failed */
+#define QG_ENOMEM (-5)
+
+/* object kinds: Sphere / Plane / TriObj (src/objects/objects.h) */
+enum { QG_OBJ_NONE = 0, QG_OBJ_SPHERE = 1, QG_OBJ_PLANE = 2, QG_OBJ_MESH = 3 };
+/* light kinds (src/lights/lights.h:35-171) */
+enum { QG_LIGHT_AMBIENT = 0, QG_LIGHT_DIRECT = 1, QG_LIGHT_POINT = 2, QG_LIGHT_SPOT = 3 };
+/* texture kinds (src/textures/texture.h): NULLTEX = a TextureMap whose file failed to load (samples black) */
+enum { QG_TEX_NULL = 0, QG_TEX_CHECKER = 1, QG_TEX_IMAGE = 2 };
+/* material kinds: MtlBlinn (alias of MtlBlinn_PhotonMap, src/materials/materials.h:57) and MultiMtl (:65-87) */
+enum { QG_MTL_BLINN = 0, QG_MTL_MULTI = 1 };
+
+/* Transformation (src/core/transform.h:36-79). Matrices column-major like glm::mat3. */
+typedef struct qgXform {
+  float tm[9];
+  float itm[9];
+  float pos[3];
+} qgXform;
+
+/* Node of the scene tree (src/core/node.h), listed in pre-order = the order Scene::TraceNodeNormal visits. */
+typedef struct qgNode {
+  int32_t parent;      /* -1 for the root (node 0, no object, identity transform) */
+  int32_t object_type; /* QG_OBJ_* */
+  int32_t mesh;        /* index into meshes[] when object_type == QG_OBJ_MESH */
+  int32_t material;    /* index into materials[] or -1 */
+  qgXform xf;
+} qgNode;
+
+/* TriMesh after TriObj::Load (src/objects/objects.h:65-73): faces already in the reference's sorted order. */
+typedef struct qgMesh {
+  const float *vertices;       /* 3 * num_vertices */
+  const float *normals;        /* 3 * num_normals */
+  const float *texcoords;      /* 2 * num_texcoords (may be NULL when 0) */
+  const int32_t *face_indices; /* 9 per face: v0 n0 t0 v1 n1 t1 v2 n2 t2; t = -1 when the corner has no uv */
+  const int32_t *face_material; /* per face material id (MultiMtl sub-material), -1 = none */
+  int32_t num_vertices, num_normals, num_texcoords, num_faces;
+  float bound_min[3], bound_max[3]; /* TriMesh::ComputeBoundingBox (TriMesh.cpp:117-133) */
+} qgMesh;
+
+/* TexturedColor + TextureMap (src/core/texture.h:55-96) */
+typedef struct qgTexturedColor {
+  float color[3];
+  int32_t texture; /* -1: no map; else index into textures[] */
+  qgXform xf;      /* the TextureMap's transformation */
+} qgTexturedColor;
+
+typedef struct qgTexture {
+  int32_t type; /* QG_TEX_* */
+  float color1[3], color2[3]; /* checker */
+  int32_t width, height;
+  const uint8_t *rgb8; /* image: width*height*3, row 0 first */
+} qgTexture;
+
+typedef struct qgMaterial {
+  int32_t kind; /* QG_MTL_* */
+  qgTexturedColor diffuse, specular, emission, reflection, refraction;
+  float absorption[3];
+  float ior;
+  float glossiness;            /* specular exponent */
+  float reflection_glossiness; /* as stored by SetReflectionGlossiness: value or -1 (MtlBlinn_PhotonMap.cpp:56-63) */
+  float refraction_glossiness;
+  float kill;                  /* russian-roulette absorb weight, 0.1 */
+  int32_t sub_first, sub_count; /* QG_MTL_MULTI: materials[multi[sub_first + mtlID]] */
+} qgMaterial;
+
+typedef struct qgLight {
+  int32_t type; /* QG_LIGHT_* */
+  float intensity[3];
+  float position[3];
+  float direction[3]; /* direct: normalised direction; spot: axis */
+  float size;
+  float inner, outer; /* spot cone in tan space (lights.cpp:121-128) */
+} qgLight;
+
+/* Camera after LoadScene (dir normalised, up re-orthogonalised; xmlload.cpp:116-144) */
+typedef struct qgCamera {
+  float pos[3], dir[3], up[3];
+  float fovy, focal, dof;
+  int32_t width, height;
+} qgCamera;
+
+typedef struct qgSceneDesc {
+  const qgNode *nodes;
+  const qgMesh *meshes;
+  const qgMaterial *materials;
+  const int32_t *multi; /* sub-material index lists of the MultiMtl entries */
+  const qgLight *lights;
+  const qgTexture *textures;
+  int32_t num_nodes, num_meshes, num_materials, num_multi, num_lights, num_textures;
+  qgTexturedColor background, environment;
+  qgCamera camera;
+} qgSceneDesc;
+
+/* DiffRay (src/core/ray.h:36-72): centre ray plus the two differential rays; has_diff = 0 for secondary rays. */
+typedef struct qgRay {
+  float p[3], dir[3];
+  float xp[3], xdir[3];
+  float yp[3], ydir[3];
+  int32_t has_diff;
+} qgRay;
+
+/* What Scene::TraceNodeNormal leaves in DiffHitInfo::c (src/core/hitinfo.h:36-52), plus the primitive id. */
+typedef struct qgHit {
+  int32_t hit;   /* 0/1 */
+  int32_t node;  /* pre-order index of hInfo.c.node, -1 on miss */
+  int32_t face;  /* face id inside the mesh (the reference's faceID into TriMesh::F), -1 for sphere/plane */
+  int32_t mtl_id;
+  int32_t front;
+  int32_t has_texture;
+  float z;
+  float p[3], N[3], uvw[3], duvw[6];
+} qgHit;
+
+typedef struct qgRenderParams {
+  int32_t spp;         /* RendererParam sppMin = sppMax (src/renderers/renderer.h:47-68, main.cpp:21-24) */
+  int32_t max_bounce;  /* Material::maxBounce (src/core/material.cpp:31), default 5 */
+  int32_t srgb;        /* RendererParam::useSRGB */
+  uint32_t seed;       /* stream seed of the counter-based RNG that replaces src/samplers */
+  int32_t width, height; /* 0 = the scene camera's; overrides <width>/<height> like editing the XML */
+  int32_t tile_rank, tile_ranks; /* Renderer::mpiRank / mpiSize: this shard renders 4x4 tiles k = rank (mod ranks) (renderer.cpp:383-387) */
+  int32_t sample_begin, sample_end; /* sample-index shard [begin,end); 0,0 = [0,spp) */
+  int32_t batch_paths; /* paths in flight per wave; 0 = default */
+  int32_t sort_by_material; /* 1 = counting-sort the shade queue by material id */
+} qgRenderParams;
+
+typedef struct qgRenderStats {
+  uint64_t samples;       /* PixelRender loop iterations */
+  uint64_t closest_rays;  /* Scene::TraceNodeNormal calls on the root */
+  uint64_t shadow_rays;   /* Scene::TraceNodeShadow calls on the root */
+  uint64_t kernel_launches;
+  uint64_t nodes_visited, tris_tested, objects_tested; /* filled by the counting build only, else 0 */
+  double device_ms;       /* CUDA-event time of the render on its stream */
+} qgRenderStats;
+
+typedef struct qgSceneInfo {
+  int32_t num_nodes, num_meshes, num_materials, num_lights, num_textures;
+  int32_t num_object_nodes;
+  int64_t num_faces, num_bvh_nodes;
+  int64_t device_bytes;
+  qgCamera camera;
+  float screen_u[3], screen_v[3], screen_a[3]; /* Renderer::ComputeScene, renderer.cpp:77-91 */
+} qgSceneInfo;
+
+typedef struct qgScene qgScene;
+
+/* Renderer::Init (src/renderers/renderer.h:101). device = CUDA ordinal. */
+int qg_init(int device);
+/* Renderer::Terminate */
+void qg_shutdown(void);
+const char *qg_last_error(void);
+
+/* LoadScene(filename) (src/parser/xmlload.cpp:71) + Renderer::ComputeScene's upload. asset_dir: directory the
+ * XML's relative .obj/.png names resolve against (the reference resolves them against the process cwd). */
+int qg_scene_load_xml(const char *xml_path, const char *asset_dir, qgScene **out);
+/* The host half of LoadScene alone (XML + OBJ + PNG -> flattened tables); needs no GPU. A binding can inspect or
+ * edit the description and hand it to qg_scene_create. */
+typedef struct qgHostScene qgHostScene;
+int qg_host_scene_load_xml(const char *xml_path, const char *asset_dir, qgHostScene **out);
+const qgSceneDesc *qg_host_scene_desc(const qgHostScene *hs);
+const char *qg_host_scene_log(const qgHostScene *hs); /* what the reference would have printed while loading */
+void qg_host_scene_destroy(qgHostScene *hs);
+/* Same, from an already flattened scene (what a C++ binding fills from qaray::Scene, src/scene/scene.h:55-67). */
+int qg_scene_create(const qgSceneDesc *desc, qgScene **out);
+void qg_scene_destroy(qgScene *scene);
+int qg_scene_info(const qgScene *scene, qgSceneInfo *out);
+/* copies the flattened node table (num_nodes entries) — lets a binding check its transforms */
+int qg_scene_nodes(const qgScene *scene, qgNode *out, int32_t capacity);
+
+/* Scene::TraceNodeNormal(rootNode, ray, hInfo) over a ray buffer (src/scene/scene.cpp:50-74). Host buffers. */
+int qg_trace_closest(qgScene *scene, const qgRay *rays, size_t n, qgHit *out);
+/* Scene::TraceNodeShadow(rootNode, ray, hInfo with z = tmax) (src/scene/scene.cpp:35-46). rays6 = p, dir. */
+int qg_trace_any(qgScene *scene, const float *rays6, const float *tmax, size_t n, uint8_t *occluded);
+/* Primary DiffRay of pixel (i,j), sample s as PixelRender builds it (renderer.cpp:312-326). pix = i,j,s triples. */
+int qg_primary_rays(qgScene *scene, const int32_t *pix, size_t n, int32_t width, int32_t height, qgRay *out);
+/* One PixelRender loop body per (i,j,s) triple: the sample's radiance before accumulation (renderer.cpp:312-339). */
+int qg_sample_radiance(qgScene *scene, const qgRenderParams *params, const int32_t *pix, size_t n, float *rgb, float *z);
+
+/* Renderer::Render for the batch renderer: ThreadRender + the FrameBuffer planes PixelRender fills
+ * (renderer.cpp:348-365). Host outputs, any may be NULL: rgb_mean W*H*3 linear means, rgb8 W*H*3,
+ * depth W*H, sample_count W*H (255*s/sppMax), mask W*H. */
+int qg_render(qgScene *scene, const qgRenderParams *params, float *rgb_mean, uint8_t *rgb8, float *depth,
+              uint8_t *sample_count, uint8_t *mask, qgRenderStats *stats);
+/* Shard render into a DEVICE accumulation buffer accum[W*H*4] = {sum R, sum G, sum B, sum weight} (+=) and
+ * depth[W*H] (written where this shard owns sample 0, else left untouched). For the multi-GPU path: every rank
+ * accumulates its tile/sample shard, the buffers are summed by one NCCL reduce (replacing the MPI_Send/Recv
+ * gather of src/renderers/Renderer_MPI.cpp:142-207), and the root resolves. stream = cudaStream_t or NULL. */
+int qg_render_accumulate(qgScene *scene, const qgRenderParams *params, float *d_accum, float *d_depth, void *stream,
+                         qgRenderStats *stats);
+/* accum (device) -> mean, sRGB, clamp, round (renderer.cpp:348-361). Host outputs as in qg_render. */
+int qg_resolve(qgScene *scene, const qgRenderParams *params, const float *d_accum, const float *d_depth,
+               float *rgb_mean, uint8_t *rgb8, float *depth, uint8_t *sample_count, uint8_t *mask, void *stream);
+
+/* FrameBuffer::SavePNG family (src/fb/framebuffer.cpp:62-143): colour, normalised depth, sample-count images. */
+int qg_save_png_rgb8(const char *path, const uint8_t *rgb8, int32_t width, int32_t height);
+int qg_save_png_depth(const char *path, const float *depth, int32_t width, int32_t height);
+int qg_save_png_gray8(const char *path, const uint8_t *gray, int32_t width, int32_t height);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* QARAY_B200_H */

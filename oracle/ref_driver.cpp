@@ -300,6 +300,39 @@ int qaref_sample(int i, int j, int s, float *rgb, float *z)
   return hasHit ? 1 : 0;
 }
 
+// Counter-based stream (needs the P4 patch of oracle/Makefile): the calling thread's sampler returns draw n of
+// the stream `key` from now on. The key derivation restates qaray_b200/csrc/qmath.h rng_key.
+static uint32_t qaref_mix(uint32_t h)
+{
+  h ^= h >> 16; h *= 0x85EBCA6Bu; h ^= h >> 13; h *= 0xC2B2AE35u; h ^= h >> 16;
+  return h;
+}
+uint32_t qaref_path_key(uint32_t pixel, uint32_t sample, uint32_t seed)
+{
+  return qaref_mix(qaref_mix(pixel * 0x9E3779B1u + 0x7F4A7C15u) ^ (sample * 0x85EBCA77u) ^ (seed * 0xC2B2AE3Du + 0x27D4EB2Fu));
+}
+void qaref_seed_path(uint32_t key)
+{
+  Sampler_Marsaglia &smp = rng->local();
+  smp.initialized = true;
+  smp.seed[0] = key;
+  smp.seed[1] = 0;
+  smp.seed[2] = 0xC0FFEE42u;
+}
+// n samples (i, j, s): the reference's own Shade recursion fed with the counter-based stream of (pixel, s, seed)
+void qaref_samples(int64_t n, const int32_t *pix, uint32_t seed, float *rgb, float *z, int32_t *hit)
+{
+  const int W = (int) g_renderer->W();
+  for (int64_t k = 0; k < n; ++k) {
+    const int i = pix[3 * k], j = pix[3 * k + 1], s = pix[3 * k + 2];
+    qaref_seed_path(qaref_path_key((uint32_t) (j * W + i), (uint32_t) s, seed));
+    float zz = 0.f;
+    const int h = qaref_sample(i, j, s, rgb + 3 * k, &zz);
+    if (z) z[k] = zz;
+    if (hit) hit[k] = h;
+  }
+}
+
 // Serial fp32 render in the reference's own pixel order (tiles of 4x4 in k order, pixels in idx order,
 // renderer.cpp:387-403) with the reference's running mean (scene.cpp:113-121); fixed spp.
 // rgb: W*H*3 linear means. Used to pin the restatement bit-for-bit (same seed, same draw order).

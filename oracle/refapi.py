@@ -48,6 +48,10 @@ class Ref:
         L.qaref_render_linear_serial.argtypes = [C.c_int, C.c_void_p, C.c_void_p]
         L.qaref_primary_ray.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p]
         L.qaref_counters.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
+        L.qaref_samples.argtypes = [C.c_int64, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.qaref_seed_path.argtypes = [C.c_uint32]
+        L.qaref_path_key.argtypes = [C.c_uint32] * 3
+        L.qaref_path_key.restype = C.c_uint32
         self.W = self.H = 0
 
     def set_params(self, spp_min, spp_max, bounce=5, srgb=True, threads=0):
@@ -114,6 +118,16 @@ class Ref:
         z = C.c_float(0)
         hit = self.lib.qaref_sample(int(i), int(j), int(s), rgb.ctypes.data_as(C.c_void_p), C.byref(z))
         return hit, rgb, z.value
+
+    def samples(self, pix_ijs, seed):
+        """radiance of single samples (i,j,s) with the counter-based stream of (pixel, s, seed) (P4 patch)"""
+        pix = np.ascontiguousarray(pix_ijs, np.int32).reshape(-1, 3)
+        rgb = np.zeros((len(pix), 3), np.float32)
+        z = np.zeros(len(pix), np.float32)
+        hit = np.zeros(len(pix), np.int32)
+        self.lib.qaref_samples(len(pix), pix.ctypes.data_as(C.c_void_p), C.c_uint32(seed), rgb.ctypes.data_as(C.c_void_p),
+                               z.ctypes.data_as(C.c_void_p), hit.ctypes.data_as(C.c_void_p))
+        return rgb, z, hit
 
     def render_linear_serial(self, spp):
         rgb = np.zeros((self.H, self.W, 3), np.float32)

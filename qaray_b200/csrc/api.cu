@@ -1,0 +1,548 @@
+// api.cu — the C ABI of include/qaray_b200.h: scene upload (host tables -> HBM), the wavefront render driver and
+// the ray-buffer entry points. Host code here is compiled with -ffp-contract=off (triangle normals and the camera
+// frame must round as the reference's glm expressions do). There is no CPU fallback: without a CUDA device every
+// compute entry point returns QG_ENODEVICE.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/qaray_b200.h"
+#include "png.h"
+#include "scene_host.h"
+#include "wavefront.h"
+
+using namespace qb;
+
+namespace {
+
+thread_local std::string g_err;
+int g_device = -1;
+
+int fail(int code, const std::string &msg)
+{
+  g_err = msg;
+  return code;
+}
+#define CU(call)                                                                                         \
+  do {                                                                                                   \
+    cudaError_t e_ = (call);                                                                             \
+    if (e_ != cudaSuccess) return fail(QG_ECUDA, std::string(#call) + ": " + cudaGetErrorString(e_));    \
+  } while (0)
+
+int ensure_device()
+{
+  if (g_device >= 0) {
+    cudaSetDevice(g_device);
+    return QG_OK;
+  }
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) return fail(QG_ENODEVICE, "no CUDA device: qaray_b200 has no CPU path");
+  g_device = 0;
+  cudaSetDevice(0);
+  return QG_OK;
+}
+
+template <class T>
+struct DevBuf {
+  T *p = nullptr;
+  size_t n = 0;
+  ~DevBuf() { release(); }
+  void release()
+  {
+    if (p) cudaFree(p);
+    p = nullptr;
+    n = 0;
+  }
+  cudaError_t alloc(size_t count)
+  {
+    release();
+    n = count;
+    return cudaMalloc((void **) &p, std::max<size_t>(count, 1) * sizeof(T));
+  }
+  cudaError_t upload(const std::vector<T> &v)
+  {
+    cudaError_t e = alloc(v.size());
+    if (e != cudaSuccess || v.empty()) return e;
+    return cudaMemcpy(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice);
+  }
+  size_t bytes() const { return n * sizeof(T); }
+};
+
+}  // namespace
+
+struct qgScene {
+  FlatScene flat;
+  DScene dev;
+  DevBuf<DNode> nodes;
+  DevBuf<int32_t> obj_node, chain_off, chain, multi;
+  DevBuf<DMesh> meshes;
+  DevBuf<DBvhNode> bvh;
+  DevBuf<DTri> tris;
+  DevBuf<uint32_t> tri_face;
+  DevBuf<DFace> faces;
+  DevBuf<DMaterial> materials;
+  DevBuf<DLight> lights;
+  DevBuf<DTexture> textures;
+  DevBuf<uchar4> texels;
+  int64_t num_faces = 0, num_bvh = 0, device_bytes = 0;
+  int num_obj = 0;
+  // wavefront buffers (allocated on first render, sized by capacity)
+  WfBuffers wf;
+  std::vector<void *> wf_allocs;
+  uint32_t wf_capacity = 0;
+  DevBuf<unsigned long long> stats;
+  cudaStream_t stream = nullptr;
+  ~qgScene()
+  {
+    for (void *p : wf_allocs) cudaFree(p);
+    if (stream) cudaStreamDestroy(stream);
+  }
+};
+
+namespace {
+
+void put_texcolor_dev(const qgTexturedColor &q, DTexColor *o)
+{
+  memset(o, 0, sizeof *o);
+  for (int k = 0; k < 3; ++k) { o->color[k] = q.color[k]; o->pos[k] = q.xf.pos[k]; }
+  o->texture = q.texture;
+  for (int k = 0; k < 9; ++k) o->itm[k] = q.xf.itm[k];
+  bool id = q.xf.pos[0] == 0.f && q.xf.pos[1] == 0.f && q.xf.pos[2] == 0.f;
+  for (int c = 0; c < 3; ++c)
+    for (int r = 0; r < 3; ++r) id = id && q.xf.itm[3 * c + r] == (c == r ? 1.f : 0.f);
+  o->identity = id ? 1 : 0;
+}
+
+int upload_scene(qgScene *sc)
+{
+  const FlatScene &F = sc->flat;
+  const int nn = (int) F.nodes.size();
+  if (nn < 1 || F.nodes[0].parent != -1) return fail(QG_EINVAL, "node 0 must be the root (parent -1)");
+  // nodes
+  std::vector<DNode> nodes(nn);
+  for (int i = 0; i < nn; ++i) {
+    const qgNode &q = F.nodes[i];
+    if (i > 0 && (q.parent < 0 || q.parent >= i)) return fail(QG_EINVAL, "nodes must be listed in pre-order (parent before child)");
+    DNode &d = nodes[i];
+    d.i0 = make_float4(q.xf.itm[0], q.xf.itm[1], q.xf.itm[2], q.xf.pos[0]);
+    d.i1 = make_float4(q.xf.itm[3], q.xf.itm[4], q.xf.itm[5], q.xf.pos[1]);
+    d.i2 = make_float4(q.xf.itm[6], q.xf.itm[7], q.xf.itm[8], q.xf.pos[2]);
+    d.t0 = make_float4(q.xf.tm[0], q.xf.tm[1], q.xf.tm[2], 0.f);
+    d.t1 = make_float4(q.xf.tm[3], q.xf.tm[4], q.xf.tm[5], 0.f);
+    d.t2 = make_float4(q.xf.tm[6], q.xf.tm[7], q.xf.tm[8], 0.f);
+    d.type = q.object_type;
+    d.mesh = q.mesh;
+    d.material = q.material;
+    d.parent = q.parent;
+    if (q.object_type == QG_OBJ_MESH && (q.mesh < 0 || q.mesh >= (int) F.meshes.size())) return fail(QG_EINVAL, "node references a missing mesh");
+    if (q.material >= (int) F.materials.size()) return fail(QG_EINVAL, "node references a missing material");
+  }
+  // object list + ancestor chains (root excluded, object node last)
+  std::vector<int32_t> obj_node, chain_off{0}, chain;
+  for (int i = 0; i < nn; ++i) {
+    if (F.nodes[i].object_type == QG_OBJ_NONE) continue;
+    std::vector<int> up;
+    for (int c = i; c > 0; c = F.nodes[c].parent) up.push_back(c);
+    if ((int) up.size() > QB_MAX_DEPTH) return fail(QG_EINVAL, "scene tree deeper than supported");
+    obj_node.push_back(i);
+    for (auto it = up.rbegin(); it != up.rend(); ++it) chain.push_back(*it);
+    chain_off.push_back((int32_t) chain.size());
+  }
+  sc->num_obj = (int) obj_node.size();
+  // meshes: BVH in the reference's topology, triangles in leaf order
+  std::vector<DMesh> meshes(F.meshes.size());
+  std::vector<DBvhNode> bvh;
+  std::vector<DTri> tris;
+  std::vector<uint32_t> tri_face;
+  std::vector<DFace> faces;
+  for (size_t mi = 0; mi < F.meshes.size(); ++mi) {
+    const qgMesh &m = F.meshes[mi];
+    ObjMesh om;
+    om.vertices.assign(m.vertices, m.vertices + 3 * (size_t) m.num_vertices);
+    om.faces.resize(m.num_faces);
+    for (int f = 0; f < m.num_faces; ++f)
+      for (int k = 0; k < 3; ++k) {
+        const int vi = m.face_indices[9 * f + 3 * k];
+        if (vi < 0 || vi >= m.num_vertices) return fail(QG_EINVAL, "mesh face references a missing vertex");
+        om.faces[f].idx[k].v = vi;
+      }
+    CyBvh cy;
+    build_cy_bvh(om, 4, &cy);  // TriObj::Load: bvh.SetMesh(this, 4) (objects.h:71)
+    DMesh &dm = meshes[mi];
+    for (int k = 0; k < 3; ++k) { dm.bmin[k] = m.bound_min[k]; dm.bmax[k] = m.bound_max[k]; }
+    dm.face_base = (uint32_t) faces.size();
+    dm.num_faces = (uint32_t) m.num_faces;
+    dm.pad = 0;
+    dm.root_ref = 0;
+    const uint32_t tri_base = (uint32_t) tris.size();
+    const uint32_t bvh_base = (uint32_t) bvh.size();
+    if ((size_t) tri_base + m.num_faces >= (1u << 28)) return fail(QG_EINVAL, "more than 2^28 triangles");
+    // triangles in leaf (elements[]) order; N = normalize(cross(B-A, C-A)) exactly as IntersectTriangle computes it
+    for (uint32_t s = 0; s < (uint32_t) m.num_faces; ++s) {
+      const uint32_t f = cy.elements[s];
+      const float *a = &m.vertices[3 * m.face_indices[9 * f + 0]], *b = &m.vertices[3 * m.face_indices[9 * f + 3]],
+                  *c = &m.vertices[3 * m.face_indices[9 * f + 6]];
+      const V3 A = v3(a[0], a[1], a[2]), B = v3(b[0], b[1], b[2]), C = v3(c[0], c[1], c[2]);
+      const V3 N = normalize(cross(B - A, C - A));
+      DTri t;
+      t.a = make_float4(A.x, A.y, A.z, N.x);
+      t.b = make_float4(B.x, B.y, B.z, N.y);
+      t.c = make_float4(C.x, C.y, C.z, N.z);
+      tris.push_back(t);
+      const bool has_uv = m.face_indices[9 * f + 2] >= 0 && m.face_indices[9 * f + 5] >= 0 && m.face_indices[9 * f + 8] >= 0;
+      tri_face.push_back((dm.face_base + f) | (has_uv ? 0x80000000u : 0u));
+    }
+    for (int f = 0; f < m.num_faces; ++f) {
+      DFace df;
+      memset(&df, 0, sizeof df);
+      bool has_uv = true;
+      for (int k = 0; k < 3; ++k) {
+        const int ni = m.face_indices[9 * f + 3 * k + 1], ti = m.face_indices[9 * f + 3 * k + 2];
+        if (ni >= 0 && ni < m.num_normals)
+          for (int c = 0; c < 3; ++c) df.n[3 * k + c] = m.normals[3 * ni + c];
+        if (ti >= 0 && ti < m.num_texcoords) { df.uv[2 * k] = m.texcoords[2 * ti]; df.uv[2 * k + 1] = m.texcoords[2 * ti + 1]; }
+        if (ti < 0) has_uv = false;
+      }
+      df.mtl_uv = ((m.face_material[f] + 1) << 1) | (has_uv ? 1 : 0);
+      faces.push_back(df);
+    }
+    if (m.num_faces > 0) {
+      // cy node id -> child ref
+      std::vector<uint32_t> internal_index(cy.nodes.size(), 0);
+      uint32_t ni = 0;
+      for (size_t id = 1; id < cy.nodes.size(); ++id)
+        if (!cy.nodes[id].leaf()) internal_index[id] = bvh_base + ni++;
+      auto ref_of = [&](uint32_t id) -> uint32_t {
+        const CyBvh::Node &n = cy.nodes[id];
+        if (n.leaf()) return QB_LEAF_BIT | ((n.count() - 1) << 28) | (tri_base + n.offset());
+        return internal_index[id];
+      };
+      bvh.resize(bvh_base + ni);
+      for (size_t id = 1; id < cy.nodes.size(); ++id) {
+        const CyBvh::Node &n = cy.nodes[id];
+        if (n.leaf()) continue;
+        const uint32_t c0 = n.child(), c1 = c0 + 1;
+        const float *b0 = cy.nodes[c0].box, *b1 = cy.nodes[c1].box;
+        DBvhNode &o = bvh[internal_index[id]];
+        o.a = make_float4(b0[0], b0[1], b0[2], b0[3]);
+        o.b = make_float4(b0[4], b0[5], b1[0], b1[1]);
+        o.c = make_float4(b1[2], b1[3], b1[4], b1[5]);
+        o.d = make_uint4(ref_of(c0), ref_of(c1), 0u, 0u);
+      }
+      dm.root_ref = ref_of(1);
+    }
+  }
+  sc->num_faces = (int64_t) faces.size();
+  sc->num_bvh = (int64_t) bvh.size();
+  // materials, lights, textures
+  std::vector<DMaterial> mats(F.materials.size());
+  for (size_t i = 0; i < mats.size(); ++i) {
+    const qgMaterial &q = F.materials[i];
+    DMaterial &d = mats[i];
+    memset(&d, 0, sizeof d);
+    d.kind = q.kind;
+    d.sub_first = q.sub_first;
+    d.sub_count = q.sub_count;
+    put_texcolor_dev(q.diffuse, &d.diffuse);
+    put_texcolor_dev(q.specular, &d.specular);
+    put_texcolor_dev(q.emission, &d.emission);
+    put_texcolor_dev(q.reflection, &d.reflection);
+    put_texcolor_dev(q.refraction, &d.refraction);
+    d.has_maps = (q.diffuse.texture >= 0 || q.specular.texture >= 0 || q.emission.texture >= 0 || q.reflection.texture >= 0 ||
+                  q.refraction.texture >= 0);
+    for (int k = 0; k < 3; ++k) d.absorption[k] = q.absorption[k];
+    d.ior = q.ior;
+    d.gloss = q.glossiness;
+    d.refl_gloss = q.reflection_glossiness;
+    d.refr_gloss = q.refraction_glossiness;
+    d.kill = q.kill;
+    if (q.kind == QG_MTL_MULTI && (q.sub_first < 0 || q.sub_first + q.sub_count > (int) F.multi.size()))
+      return fail(QG_EINVAL, "multi-material list out of range");
+  }
+  for (int32_t s : F.multi)
+    if (s < 0 || s >= (int) mats.size()) return fail(QG_EINVAL, "multi-material entry out of range");
+  std::vector<DLight> lights(F.lights.size());
+  int nonambient = 0;
+  for (size_t i = 0; i < lights.size(); ++i) {
+    const qgLight &q = F.lights[i];
+    DLight &d = lights[i];
+    d.type = q.type;
+    for (int k = 0; k < 3; ++k) { d.intensity[k] = q.intensity[k]; d.position[k] = q.position[k]; d.direction[k] = q.direction[k]; }
+    d.size = q.size;
+    d.inner = q.inner;
+    d.outer = q.outer;
+    if (q.type != QG_LIGHT_AMBIENT) ++nonambient;
+  }
+  std::vector<DTexture> texs(F.textures.size());
+  std::vector<uchar4> texels;
+  for (size_t i = 0; i < texs.size(); ++i) {
+    const qgTexture &q = F.textures[i];
+    DTexture &d = texs[i];
+    memset(&d, 0, sizeof d);
+    d.type = q.type;
+    d.width = q.width;
+    d.height = q.height;
+    for (int k = 0; k < 3; ++k) { d.c1[k] = q.color1[k]; d.c2[k] = q.color2[k]; }
+    d.texel_base = (uint32_t) texels.size();
+    if (q.type == QG_TEX_IMAGE) {
+      if (!q.rgb8 || q.width <= 0 || q.height <= 0) return fail(QG_EINVAL, "image texture without pixels");
+      const size_t np = (size_t) q.width * q.height;
+      for (size_t p = 0; p < np; ++p) texels.push_back(make_uchar4(q.rgb8[3 * p], q.rgb8[3 * p + 1], q.rgb8[3 * p + 2], 255));
+    }
+  }
+  auto tex_ok = [&](const qgTexturedColor &t) { return t.texture < (int) texs.size(); };
+  for (const qgMaterial &q : F.materials)
+    if (!tex_ok(q.diffuse) || !tex_ok(q.specular) || !tex_ok(q.emission) || !tex_ok(q.reflection) || !tex_ok(q.refraction))
+      return fail(QG_EINVAL, "material references a missing texture");
+  if (!tex_ok(F.background) || !tex_ok(F.environment)) return fail(QG_EINVAL, "background/environment references a missing texture");
+
+  CU(sc->nodes.upload(nodes));
+  CU(sc->obj_node.upload(obj_node));
+  CU(sc->chain_off.upload(chain_off));
+  CU(sc->chain.upload(chain));
+  CU(sc->meshes.upload(meshes));
+  CU(sc->bvh.upload(bvh));
+  CU(sc->tris.upload(tris));
+  CU(sc->tri_face.upload(tri_face));
+  CU(sc->faces.upload(faces));
+  CU(sc->materials.upload(mats));
+  CU(sc->multi.upload(F.multi));
+  CU(sc->lights.upload(lights));
+  CU(sc->textures.upload(texs));
+  CU(sc->texels.upload(texels));
+  CU(sc->stats.alloc(8));
+  CU(cudaMemset(sc->stats.p, 0, sc->stats.bytes()));
+  sc->device_bytes = (int64_t) (sc->nodes.bytes() + sc->obj_node.bytes() + sc->chain_off.bytes() + sc->chain.bytes() + sc->meshes.bytes() +
+                                sc->bvh.bytes() + sc->tris.bytes() + sc->tri_face.bytes() + sc->faces.bytes() + sc->materials.bytes() +
+                                sc->multi.bytes() + sc->lights.bytes() + sc->textures.bytes() + sc->texels.bytes());
+  DScene &D = sc->dev;
+  memset(&D, 0, sizeof D);
+  D.nodes = sc->nodes.p; D.obj_node = sc->obj_node.p; D.chain_off = sc->chain_off.p; D.chain = sc->chain.p;
+  D.meshes = sc->meshes.p; D.bvh = sc->bvh.p; D.tris = sc->tris.p; D.tri_face = sc->tri_face.p; D.faces = sc->faces.p;
+  D.materials = sc->materials.p; D.multi = sc->multi.p; D.lights = sc->lights.p; D.textures = sc->textures.p; D.texels = sc->texels.p;
+  D.num_nodes = nn; D.num_obj = sc->num_obj; D.num_meshes = (int) meshes.size(); D.num_materials = (int) mats.size();
+  D.num_lights = (int) lights.size(); D.num_textures = (int) texs.size(); D.num_nonambient = nonambient;
+  put_texcolor_dev(F.background, &D.background);
+  put_texcolor_dev(F.environment, &D.environment);
+  // Texture::Sample's tap table (core/texture.cpp:38-49): Halton(2,3) points mapped onto the unit-diameter disc
+  float taps[64];
+  taps[0] = taps[1] = 0.f;
+  for (int i = 1; i < 32; ++i) {
+    float x = halton(i, 2), y = halton(i, 3);
+    const float r = sqrtf(x) * 0.5f;
+    x = r * sinf(y * (float) M_PI * 2);
+    y = r * cosf(y * (float) M_PI * 2);
+    taps[2 * i] = x;
+    taps[2 * i + 1] = y;
+  }
+  upload_texture_taps(taps);
+  CU(cudaStreamCreateWithFlags(&sc->stream, cudaStreamNonBlocking));
+  CU(cudaDeviceSynchronize());
+  return QG_OK;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------- render driver
+namespace {
+
+int ensure_wf(qgScene *sc, uint32_t capacity)
+{
+  if (sc->wf_capacity == capacity) return QG_OK;
+  for (void *p : sc->wf_allocs) cudaFree(p);
+  sc->wf_allocs.clear();
+  sc->wf_capacity = 0;
+  WfBuffers &B = sc->wf;
+  memset(&B, 0, sizeof B);
+  auto alloc4 = [&](float4 **p, size_t n) -> cudaError_t {
+    cudaError_t e = cudaMalloc((void **) p, std::max<size_t>(n, 1) * sizeof(float4));
+    if (e == cudaSuccess) sc->wf_allocs.push_back(*p);
+    return e;
+  };
+  const size_t shadow_cap = (size_t) capacity * (size_t) std::max(1, sc->dev.num_nonambient);
+  for (int k = 0; k < 2; ++k) {
+    CU(alloc4(&B.ps0[k], capacity));
+    CU(alloc4(&B.ps1[k], capacity));
+    CU(alloc4(&B.ps2[k], capacity));
+    CU(alloc4(&B.ps3[k], capacity));
+  }
+  CU(alloc4(&B.h0, capacity));
+  CU(alloc4(&B.h1, capacity));
+  CU(alloc4(&B.h2, capacity));
+  CU(alloc4(&B.h3, capacity));
+  CU(alloc4(&B.s0, shadow_cap));
+  CU(alloc4(&B.s1, shadow_cap));
+  CU(alloc4(&B.s2, shadow_cap));
+  CU(cudaMalloc((void **) &B.counters, QB_CNT_WORDS * sizeof(uint32_t)));
+  sc->wf_allocs.push_back(B.counters);
+  B.stats = sc->stats.p;
+  B.capacity = capacity;
+  B.shadow_capacity = (uint32_t) std::min<size_t>(shadow_cap, 0xFFFFFFFFu);
+  sc->wf_capacity = capacity;
+  return QG_OK;
+}
+
+// Renderer::ComputeScene's camera frame (renderer.cpp:77-91)
+void camera_frame(const qgCamera &cam, int W, int H, V3 *U, V3 *Vv, V3 *A)
+{
+  const float PI = (float) M_PI;
+  const V3 pos = v3(cam.pos[0], cam.pos[1], cam.pos[2]), dir = v3(cam.dir[0], cam.dir[1], cam.dir[2]), up = v3(cam.up[0], cam.up[1], cam.up[2]);
+  const float focal = cam.focal;
+  const float aspect = W / (float) H;
+  const float screenH = 2.f * focal * std::tan(cam.fovy * PI / 2.f / 180.f);
+  const float screenW = aspect * screenH;
+  const V3 X = normalize(cross(dir, up));
+  const V3 Y = normalize(cross(X, dir));
+  const V3 Z = normalize(-dir);
+  *U = X * (screenW / W);
+  *Vv = -Y * (screenH / H);
+  *A = pos - Z * focal + Y * screenH / 2.f - X * screenW / 2.f;
+}
+
+struct Shard {
+  int W, H, tiles_x, tiles_y, tiles_local, s0, s1;
+  unsigned long long total_paths, valid_samples;
+};
+
+int make_params(const qgScene *sc, const qgRenderParams *rp, WfParams *P, Shard *sh)
+{
+  if (!rp || rp->spp <= 0) return fail(QG_EINVAL, "spp must be positive");
+  if (rp->max_bounce < 0 || rp->max_bounce >= QB_MAX_BOUNCE) return fail(QG_EINVAL, "max_bounce out of range [0, 14]");
+  const qgCamera &cam = sc->flat.camera;
+  const int W = rp->width > 0 ? rp->width : cam.width, H = rp->height > 0 ? rp->height : cam.height;
+  if (W <= 0 || H <= 0) return fail(QG_EINVAL, "image size must be positive");
+  const int ranks = rp->tile_ranks > 0 ? rp->tile_ranks : 1;
+  if (rp->tile_rank < 0 || rp->tile_rank >= ranks) return fail(QG_EINVAL, "tile_rank out of range");
+  int s0 = rp->sample_begin, s1 = rp->sample_end;
+  if (s0 == 0 && s1 == 0) s1 = rp->spp;
+  if (s0 < 0 || s1 > rp->spp || s0 > s1) return fail(QG_EINVAL, "sample shard out of range");
+  memset(P, 0, sizeof *P);
+  camera_frame(cam, W, H, &P->scr_u, &P->scr_v, &P->scr_a);
+  P->cam_pos = v3(cam.pos[0], cam.pos[1], cam.pos[2]);
+  P->width = W;
+  P->height = H;
+  P->mode = 0;
+  sh->W = W;
+  sh->H = H;
+  sh->tiles_x = (W + 3) / 4;  // tileDimX = ceil(W / tileSize), tileSize = 4 (renderer.h:93, renderer.cpp:104-108)
+  sh->tiles_y = (H + 3) / 4;
+  const int tile_count = sh->tiles_x * sh->tiles_y;
+  sh->tiles_local = tile_count > rp->tile_rank ? (tile_count - rp->tile_rank + ranks - 1) / ranks : 0;
+  sh->s0 = s0;
+  sh->s1 = s1;
+  sh->total_paths = (unsigned long long) sh->tiles_local * 16ull * (unsigned long long) (s1 - s0);
+  // pixels this shard really owns (edge tiles are partly outside the image)
+  unsigned long long px = 0;
+  for (int lt = 0; lt < sh->tiles_local; ++lt) {
+    const int k = rp->tile_rank + lt * ranks, tx = k % sh->tiles_x, ty = k / sh->tiles_x;
+    px += (unsigned long long) (std::min(W, tx * 4 + 4) - tx * 4) * (unsigned long long) (std::min(H, ty * 4 + 4) - ty * 4);
+  }
+  sh->valid_samples = px * (unsigned long long) (s1 - s0);
+  P->tiles_x = sh->tiles_x;
+  P->tile_rank = rp->tile_rank;
+  P->tile_ranks = ranks;
+  P->tiles_local = sh->tiles_local;
+  P->sample_begin = s0;
+  P->seed = rp->seed;
+  P->max_bounce = rp->max_bounce;
+  P->stale_tex = 1;
+  return QG_OK;
+}
+
+// one wave: depth loop of trace -> shade -> shadow, all on `st`, no host synchronisation
+void run_wave(qgScene *sc, WfParams P, cudaStream_t st, uint64_t *launches)
+{
+  const WfBuffers &B = sc->wf;
+  cudaMemsetAsync(B.counters, 0, QB_CNT_WORDS * sizeof(uint32_t), st);
+  const int gt = wf_trace_grid(), gs = wf_shade_grid(), gsh = wf_shadow_grid();
+  for (int d = 0; d <= P.max_bounce; ++d) {
+    P.depth = d;
+    launch_wf_trace(sc->dev, B, P, gt, st);
+    launch_wf_shade(sc->dev, B, P, gs, st);
+    *launches += 2;
+    if (sc->dev.num_nonambient > 0) {
+      launch_wf_shadow(sc->dev, B, P, gsh, st);
+      *launches += 1;
+    }
+  }
+  launch_wf_stats(B, P.max_bounce, st);
+  *launches += 1;
+}
+
+int render_accumulate(qgScene *sc, const qgRenderParams *rp, float *d_accum, float *d_depth, cudaStream_t st, qgRenderStats *stats)
+{
+  WfParams P;
+  Shard sh;
+  int rc = make_params(sc, rp, &P, &sh);
+  if (rc) return rc;
+  uint32_t cap = rp->batch_paths > 0 ? (uint32_t) rp->batch_paths : (1u << 21);
+  cap = (cap + 31u) & ~31u;
+  if ((unsigned long long) cap > sh.total_paths) cap = (uint32_t) std::max<unsigned long long>(32ull, (sh.total_paths + 31ull) & ~31ull);
+  rc = ensure_wf(sc, cap);
+  if (rc) return rc;
+  P.accum = d_accum;
+  P.depth_plane = d_depth;
+  cudaEvent_t e0, e1;
+  CU(cudaEventCreate(&e0));
+  CU(cudaEventCreate(&e1));
+  CU(cudaMemsetAsync(sc->stats.p, 0, sc->stats.bytes(), st));
+  CU(cudaEventRecord(e0, st));
+  uint64_t launches = 0;
+  for (unsigned long long base = 0; base < sh.total_paths; base += cap) {
+    P.wave_base = base;
+    P.n_paths = (uint32_t) std::min<unsigned long long>(cap, sh.total_paths - base);
+    run_wave(sc, P, st, &launches);
+  }
+  CU(cudaEventRecord(e1, st));
+  CU(cudaStreamSynchronize(st));
+  CU(cudaGetLastError());
+  if (stats) {
+    unsigned long long hs[8];
+    CU(cudaMemcpy(hs, sc->stats.p, sizeof hs, cudaMemcpyDeviceToHost));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    memset(stats, 0, sizeof *stats);
+    stats->samples = sh.valid_samples;
+    stats->closest_rays = hs[0] + sh.valid_samples;
+    stats->shadow_rays = hs[1];
+    stats->nodes_visited = hs[2];
+    stats->tris_tested = hs[3];
+    stats->objects_tested = hs[4];
+    stats->kernel_launches = launches;
+    stats->device_ms = ms;
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  return QG_OK;
+}
+
+int resolve_to_host(qgScene *sc, int W, int H, int spp, int srgb, const float *d_accum, const float *d_depth, float *rgb_mean, uint8_t *rgb8,
+                    float *depth, uint8_t *sample_count, uint8_t *mask, cudaStream_t st)
+{
+  const size_t n = (size_t) W * H;
+  DevBuf<float> d_mean, d_dep;
+  DevBuf<uint8_t> d_rgb8, d_sc, d_mask;
+  if (rgb_mean) CU(d_mean.alloc(3 * n));
+  if (rgb8) CU(d_rgb8.alloc(3 * n));
+  if (depth) CU(d_dep.alloc(n));
+  if (sample_count) CU(d_sc.alloc(n));
+  if (mask) CU(d_mask.alloc(n));
+  launch_resolve(d_accum, d_depth, (int) n, spp, srgb, d_mean.p, d_rgb8.p, d_dep.p, d_sc.p, d_mask.p, st);
+  if (rgb_mean) CU(cudaMemcpyAsync(rgb_mean, d_mean.p, 3 * n * sizeof(float), cudaMemcpyDeviceToHost, st));
+  if (rgb8) CU(cudaMemcpyAsync(rgb8, d_rgb8.p, 3 * n, cudaMemcpyDeviceToHost, st));
+  if (depth) CU(cudaMemcpyAsync(depth, d_dep.p, n * sizeof(float), cudaMemcpyDeviceToHost, st));
+  if (sample_count) CU(cudaMemcpyAsync(sample_count, d_sc.p, n, cudaMemcpyDeviceToHost, st));
+  if (mask) CU(cudaMemcpyAsync(mask, d_mask.p, n, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  CU(cudaGetLastError());
+  return QG_OK;
+}
+
+}  // namespace
+
+#include "api_entry.inc"  // the extern "C" entry points

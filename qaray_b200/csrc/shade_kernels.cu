@@ -1,0 +1,449 @@
+// shade_kernels.cu — material evaluation, BSDF sampling, next-event estimation and frame resolve (sm_100a).
+//
+//   k_wf_shade   MtlBlinn_PhotonMap::Shade with photon mapping off (src/materials/MtlBlinn_PhotonMap.cpp:256-500),
+//                the material class the reference compiles in (src/materials/materials.h:57), turned from a
+//                recursion into one step of a throughput-carrying path:
+//                    radiance += T * (emission + sum_lights direct)          (direct via the shadow queue)
+//                    T'        = T * BxDF  (x exp(-absorption * z) when the next hit is a back face, :246-248)
+//                MultiMtl dispatch (materials.h:70-76), lights (src/lights/lights.cpp:18-144),
+//                textures (src/core/texture.cpp:32-114, src/textures/texture.cpp:97-137),
+//                sampling distributions (src/core/sampler.cpp:42-120, src/math/math.cpp:37-46).
+//   k_resolve    mean, sRGB, clamp, round to 8 bit (src/renderers/renderer.cpp:34-39,348-365).
+//
+// Random numbers: a counter-based stream per (pixel, sample) drawn in the order the reference's recursion draws
+// them (lobe selection, then the lobe's direction sample, then the next hit...), so the same stream fed to the
+// reference gives the same path.
+#include "wavefront.h"
+
+namespace qb {
+
+__constant__ float2 c_taps[32];
+
+void upload_texture_taps(const float *xy64) { cudaMemcpyToSymbol(c_taps, xy64, sizeof(float2) * 32); }
+
+struct Rng {
+  uint32_t key, n;
+  __device__ __forceinline__ float next() { return rng_float(key, n++); }
+};
+
+__device__ __forceinline__ V3 ld3(const float *p) { return v3(p[0], p[1], p[2]); }
+
+// ---- textures ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ V3 tile_clamp(V3 uvw)  // Texture::TileClamp, core/texture.cpp:53-63
+{
+  V3 u = v3(uvw.x - (float) (int) uvw.x, uvw.y - (float) (int) uvw.y, uvw.z - (float) (int) uvw.z);
+  if (u.x < 0) u.x += 1;
+  if (u.y < 0) u.y += 1;
+  if (u.z < 0) u.z += 1;
+  return u;
+}
+
+__device__ __forceinline__ V3 texel(const DScene &S, const DTexture &t, int x, int y)
+{
+  const uchar4 c = __ldg(&S.texels[t.texel_base + (uint32_t) y * (uint32_t) t.width + (uint32_t) x]);
+  return v3(c.x / 255.0f, c.y / 255.0f, c.z / 255.0f);
+}
+
+__device__ V3 texture_fetch(const DScene &S, const DTexture &t, V3 uvw)
+{
+  if (t.type == QG_TEX_CHECKER) {  // TextureChecker::Sample, textures/texture.cpp:129-137
+    const V3 u = tile_clamp(uvw);
+    const V3 c1 = ld3(t.c1), c2 = ld3(t.c2);
+    if (u.x <= 0.5f) return u.y <= 0.5f ? c1 : c2;
+    return u.y <= 0.5f ? c2 : c1;
+  }
+  if (t.type != QG_TEX_IMAGE || t.width + t.height == 0) return v3(0.f);
+  // TextureFile::Sample, textures/texture.cpp:97-125: v flipped, tiled, bilinear
+  const V3 u = tile_clamp(v3(uvw.x, 1.f - uvw.y, uvw.z));
+  const int width = t.width, height = t.height;
+  const float x = width * u.x;
+  const float y = height * u.y;
+  int ix = (int) x, iy = (int) y;
+  const float fx = x - ix, fy = y - iy;
+  if (ix < 0) ix -= (ix / width - 1) * width;
+  if (ix >= width) ix -= (ix / width) * width;
+  int ixp = ix + 1;
+  if (ixp >= width) ixp -= width;
+  if (iy < 0) iy -= (iy / height - 1) * height;
+  if (iy >= height) iy -= (iy / height) * height;
+  int iyp = iy + 1;
+  if (iyp >= height) iyp -= height;
+  return texel(S, t, ix, iy) * ((1 - fx) * (1 - fy)) + texel(S, t, ixp, iy) * (fx * (1 - fy)) + texel(S, t, ix, iyp) * ((1 - fx) * fy) +
+         texel(S, t, ixp, iyp) * (fx * fy);
+}
+
+__device__ __forceinline__ V3 texmap_to(const DTexColor &tc, V3 p)  // TextureMap's Transformation::TransformTo
+{
+  if (tc.identity) return p;
+  const V3 a = p - ld3(tc.pos);
+  return v3(tc.itm[0] * a.x + tc.itm[3] * a.y + tc.itm[6] * a.z, tc.itm[1] * a.x + tc.itm[4] * a.y + tc.itm[7] * a.z,
+            tc.itm[2] * a.x + tc.itm[5] * a.y + tc.itm[8] * a.z);
+}
+
+// TexturedColor::Sample(uvw) — single tap (background, environment)
+__device__ V3 texcolor_sample1(const DScene &S, const DTexColor &tc, V3 uvw)
+{
+  const V3 color = ld3(tc.color);
+  if (tc.texture < 0) return color;
+  return color * texture_fetch(S, S.textures[tc.texture], texmap_to(tc, uvw));
+}
+
+// Sample(hInfo, TexturedColor) of MtlBlinn_PhotonMap.cpp:34-39 -> TexturedColor::Sample(uvw, duvw, elliptic=true)
+// -> TextureMap::Sample -> Texture::Sample: 1 tap, or 32 taps on the ellipse spanned by duvw when duvw != 0
+__device__ V3 texcolor_sample(const DScene &S, const DTexColor &tc, bool has_texture, V3 uvw, V3 d0, V3 d1)
+{
+  const V3 color = ld3(tc.color);
+  if (tc.texture < 0 || !has_texture) return color;
+  const DTexture &t = S.textures[tc.texture];
+  const V3 u = texmap_to(tc, uvw);
+  const V3 e0 = texmap_to(tc, d0 + uvw) - u;
+  const V3 e1 = texmap_to(tc, d1 + uvw) - u;
+  V3 c = texture_fetch(S, t, u);
+  if (length2(e0) + length2(e1) == 0) return color * c;
+  for (int i = 1; i < 32; ++i) {
+    const float2 xy = c_taps[i];
+    c += texture_fetch(S, t, u + xy.x * e0 + xy.y * e1);
+  }
+  return color * (c / 32.f);
+}
+
+__device__ V3 sample_environment(const DScene &S, V3 dir)  // TexturedColor::SampleEnvironment, core/texture.cpp:107-114
+{
+  const float z = asinf(-dir.z) / 3.14159274101257324f + 0.5f;
+  const float x = dir.x / (qabs(dir.x) + qabs(dir.y));
+  const float y = dir.y / (qabs(dir.x) + qabs(dir.y));
+  return texcolor_sample1(S, S.environment, v3(0.5f, 0.5f, 0.0f) + z * (x * v3(0.5f, 0.5f, 0.f) + y * v3(-0.5f, 0.5f, 0.f)));
+}
+
+// ---- sampling distributions --------------------------------------------------------------------------------------
+__device__ __forceinline__ V3 to_local_frame(V3 N, V3 sample)  // TransformToLocalFrame, math/math.cpp:37-46
+{
+  const V3 Z = N;
+  const V3 Y = (qabs(Z.x) > qabs(Z.y)) ? normalize(v3(Z.z, 0, -Z.x)) : normalize(v3(0, -Z.z, Z.y));
+  const V3 X = normalize(cross(Y, Z));
+  const V3 unit = normalize(sample);
+  return unit.x * X + unit.y * Y + unit.z * Z;
+}
+__device__ __forceinline__ V3 cos_weighted_hemisphere(Rng &rng)  // core/sampler.cpp:91-107
+{
+  const float r1 = rng.next(), r2 = rng.next();
+  const float cosTheta = sqrtf(r1);
+  const float sinTheta = sqrtf(1 - r1);
+  const float phi = 2 * 3.14159274101257324f * r2;
+  return v3(sinTheta * cosf(phi), sinTheta * sinf(phi), cosTheta);
+}
+// Sampler::UniformBall (core/sampler.cpp:42-53): rejection from the cube; z reuses r2 as the reference does.
+// The reference loops without bound; 64 rounds leave a miss probability below 1e-20.
+__device__ __forceinline__ V3 uniform_ball(Rng &rng, float radius)
+{
+  V3 p = v3(0.f);
+  for (int it = 0; it < 64; ++it) {
+    const float r1 = rng.next(), r2 = rng.next(), r3 = rng.next();
+    (void) r3;
+    p = v3((2.f * r1 - 1.f) * radius, (2.f * r2 - 1.f) * radius, (2.f * r2 - 1.f) * radius);
+    if (!(length(p) > radius)) break;
+  }
+  return p;
+}
+
+// SpotLight::GetAttenuation, lights.cpp:128-144
+__device__ __forceinline__ float spot_attenuation(const DLight &l, V3 dir)
+{
+  const float cosTheta = dot(dir, ld3(l.direction));
+  if (cosTheta < 0) return 0.f;
+  const float r = sqrtf(1.f - cosTheta * cosTheta) / cosTheta;
+  if (r > l.outer) return 0.f;
+  if (r < l.inner) return 1.f;
+  const float q = (l.outer - r) / (l.outer - l.inner);
+  return q * q;  // POW(x, 2.f)
+}
+
+enum { SEL_TRANSMIT = 0, SEL_REFLECT = 1, SEL_DIFFUSE = 2, SEL_ABSORB = 3 };
+
+#define QB_FLAG_DIFFUSE_HIT 1u
+
+__device__ __forceinline__ void accum_add(float *accum, int slot, V3 c)
+{
+  float *a = accum + 4ll * slot;
+  atomicAdd(a + 0, c.x);
+  atomicAdd(a + 1, c.y);
+  atomicAdd(a + 2, c.z);
+}
+
+__global__ void __launch_bounds__(QB_BLOCK) k_wf_shade(const DScene S, const WfBuffers B, const WfParams P)
+{
+  const int d = P.depth;
+  const uint32_t n = d == 0 ? P.n_paths : B.counters[QB_CNT_PATHS + d];
+  const int bounce_count = P.max_bounce - d;
+  const int lane = threadIdx.x & 31;
+  const uint32_t lt_mask = (1u << lane) - 1u;
+  const int pb = d & 1, nb = pb ^ 1;
+  const float color_luma_threshold = 0.00001f;
+  for (;;) {
+    uint32_t base = 0;
+    if (lane == 0) base = atomicAdd(&B.counters[QB_CNT_FETCH_SHADE + d], 32u);
+    base = __shfl_sync(0xFFFFFFFFu, base, 0);
+    if (base >= n) break;
+    const uint32_t idx = base + lane;
+
+    bool do_lights = false, alive = false;
+    V3 p = v3(0.f), N = v3(0.f), V = v3(0.f), T = v3(1.f), Kd = v3(0.f), Ks = v3(0.f);
+    float gloss = 0.f;
+    int slot = 0;
+    // next path
+    V3 next_dir = v3(0.f), next_T = v3(0.f), next_absorb = v3(0.f);
+    uint32_t next_flags = 0;
+    Rng rng = {0u, 0u};
+
+    if (idx < n) {
+      const float4 h0 = B.h0[idx];
+      const int node = __float_as_int(h0.y);
+      V3 ray_dir;
+      V3 absorb_prev = v3(0.f);
+      uint32_t flags = 0;
+      bool valid = true;
+      if (d == 0) {
+        int i, j, s;
+        valid = wf_decode(P, idx, i, j, s, slot);
+        if (valid) {
+          rng.key = rng_key((uint32_t) (j * P.width + i), (uint32_t) s, P.seed);
+          atomicAdd(P.accum + 4ll * slot + 3, 1.0f);
+          if (P.depth_plane && (s == 0 || P.mode == 1)) P.depth_plane[slot] = node >= 0 ? h0.x : QB_BIGFLOAT;
+          if (node < 0) {  // background by screen position (renderer.cpp:336-338)
+            const float tx = halton(s, 11) + (float) i, ty = halton(s, 13) + (float) j;
+            accum_add(P.accum, slot, texcolor_sample1(S, S.background, v3(tx / (float) P.width, ty / (float) P.height, 0.f)));
+          } else {
+            const float tx = halton(s, 11) + (float) i, ty = halton(s, 13) + (float) j;
+            const V3 cpt = P.scr_a + tx * P.scr_u + ty * P.scr_v;
+            ray_dir = normalize(cpt - P.cam_pos);
+          }
+        }
+      } else {
+        const float4 a = B.ps0[pb][idx], b = B.ps1[pb][idx], c = B.ps2[pb][idx], e = B.ps3[pb][idx];
+        ray_dir = v3(a.w, b.x, b.y);
+        slot = __float_as_int(b.z);
+        rng.key = __float_as_uint(b.w);
+        T = v3(c.x, c.y, c.z);
+        const uint32_t packed = __float_as_uint(c.w);
+        rng.n = packed >> 8;
+        flags = packed & 0xFFu;
+        absorb_prev = v3(e.x, e.y, e.z);
+        if (node < 0) accum_add(P.accum, slot, T * sample_environment(S, ray_dir));  // ComputeSecondaryRay miss (:250)
+      }
+      if (valid && node >= 0) {
+        const float4 h1 = B.h1[idx], h2 = B.h2[idx], h3 = B.h3[idx];
+        const float z = h0.x;
+        const int mtl_id = __float_as_int(h0.z);
+        const int hflags = __float_as_int(h0.w);
+        const bool front = hflags & 1, has_tex = hflags & 2;
+        p = v3(h1.x, h1.y, h1.z);
+        N = v3(h1.w, h2.x, h2.y);
+        const V3 uvw = v3(h2.z, h2.w, 0.f);
+        const V3 d0 = v3(h3.x, h3.y, 0.f), d1 = v3(h3.z, h3.w, 0.f);
+        // Beer-Lambert over the segment that ended on a back face (MtlBlinn_PhotonMap.cpp:246-248, materials.cpp:32-38)
+        if (d > 0 && !front) T = T * v3(expf(-absorb_prev.x * z), expf(-absorb_prev.y * z), expf(-absorb_prev.z * z));
+        int mi = S.nodes[node].material;
+        bool white = false;
+        if (mi >= 0 && S.materials[mi].kind == QG_MTL_MULTI) {  // MultiMtl::Shade
+          const DMaterial &mm = S.materials[mi];
+          if (mtl_id >= 0 && mtl_id < mm.sub_count) mi = S.multi[mm.sub_first + mtl_id];
+          else white = true;
+        }
+        if (white) {
+          accum_add(P.accum, slot, T);
+        } else if (mi >= 0) {
+          const DMaterial &M = S.materials[mi];
+          V = -ray_dir;
+          V3 color = texcolor_sample(S, M.emission, has_tex, uvw, d0, d1);
+          // ComputeFresnel (:65-105)
+          const V3 Y = dot(N, V) > 0.f ? N : -N;
+          const V3 Zf = cross(V, Y);
+          const V3 X = normalize(cross(Y, Zf));
+          const float nIOR = front ? 1.f / M.ior : M.ior;
+          const float cosI = dot(N, V);
+          const float sinI = sqrtf(1 - cosI * cosI);
+          const float sinO = qmax(0.f, qmin(1.f, sinI * nIOR));
+          const float cosO = sqrtf(1.f - sinO * sinO);
+          const V3 tDir = -X * sinO - Y * cosO;
+          const V3 rDir = 2.f * N * (dot(N, V)) - V;
+          const bool total_reflection = (nIOR * sinI) > 1.001f;
+          const float C = (nIOR - 1.f) * (nIOR - 1.f) / ((nIOR + 1.f) * (nIOR + 1.f));
+          const float rC = C + (1.f - C) * powf(1.f - qabs(cosI), 5.f);
+          const float tC = 1.f - rC;
+          const V3 tK = texcolor_sample(S, M.refraction, has_tex, uvw, d0, d1);
+          const V3 rK = texcolor_sample(S, M.reflection, has_tex, uvw, d0, d1);
+          const V3 sT = total_reflection ? v3(0.f) : tK * tC;
+          const V3 sR = total_reflection ? (rK + tK) : (rK + tK * rC);
+          Ks = texcolor_sample(S, M.specular, has_tex, uvw, d0, d1);
+          Kd = texcolor_sample(S, M.diffuse, has_tex, uvw, d0, d1);
+          gloss = M.gloss;
+          // RandomSelectMtl (:107-150)
+          const float lumaT = luma(sT), lumaR = luma(sR), lumaD = luma(Kd);
+          const float r = rng.next();
+          const float coefT = lumaT, coefR = coefT + lumaR, coefD = coefR + lumaD, coefSum = coefD + M.kill;
+          const float select = r * coefSum;
+          int sel;
+          if (select < coefT && lumaT > color_luma_threshold) sel = SEL_TRANSMIT;
+          else if (select < coefR && lumaR > color_luma_threshold) sel = SEL_REFLECT;
+          else if (select < coefD && lumaD > color_luma_threshold) sel = SEL_DIFFUSE;
+          else sel = SEL_ABSORB;
+          if (bounce_count > 0) {
+            if (sel == SEL_REFLECT) {  // SampleReflectionBxDF (:179-203)
+              V3 dir = rDir;
+              if (M.refl_gloss > 0.f) {
+                for (int it = 0; it < 64; ++it) {
+                  dir = normalize(normalize(rDir) + uniform_ball(rng, 2.f * M.refl_gloss));
+                  if (!(dot(dir, Y) < 0)) break;
+                }
+              }
+              alive = true; next_dir = dir; next_T = T * sR;
+            } else if (sel == SEL_TRANSMIT) {  // SampleTransmitBxDF (:152-178)
+              V3 dir = tDir;
+              if (M.refr_gloss > 0.f) {
+                for (int it = 0; it < 64; ++it) {
+                  dir = normalize(normalize(tDir) + uniform_ball(rng, 2.f * M.refr_gloss));
+                  if (!(dot(dir, Y) > 0)) break;
+                }
+              }
+              alive = true; next_dir = dir; next_T = T * sT;
+            } else if (sel == SEL_DIFFUSE && !(flags & QB_FLAG_DIFFUSE_HIT) && front) {  // SampleDiffuseBxDF (:204-224)
+              const V3 dir = to_local_frame(N, cos_weighted_hemisphere(rng));
+              const V3 L = normalize(dir);
+              const V3 H = normalize(V + L);
+              const float cosNH = qmax(0.f, dot(N, H));
+              alive = true; next_dir = dir; next_T = T * (Kd + Ks * powf(cosNH, gloss));
+              next_flags = QB_FLAG_DIFFUSE_HIT;
+            }
+          }
+          next_absorb = ld3(M.absorption);
+          accum_add(P.accum, slot, T * color);
+          do_lights = true;
+        }
+      }
+    }
+
+    // ---- next-event estimation: one shadow ray per non-ambient light (:484-498), warp-aggregated queue push
+    const float norm_di = S.num_lights > 0 ? 1.f / (float) S.num_lights : 1.f;
+    for (int l = 0; l < S.num_lights; ++l) {
+      const DLight &lt = S.lights[l];
+      if (lt.type == QG_LIGHT_AMBIENT) continue;  // uniform across the warp
+      bool push = false;
+      V3 sdir = v3(0.f), contrib = v3(0.f);
+      float tmax = QB_BIGFLOAT;
+      if (do_lights) {
+        V3 I = ld3(lt.intensity), Ldir;
+        if (lt.type == QG_LIGHT_DIRECT) {
+          sdir = normalize(-ld3(lt.direction));
+          Ldir = ld3(lt.direction);
+        } else {
+          const V3 dv = ld3(lt.position) - p;
+          sdir = normalize(dv);
+          tmax = length(dv);
+          I = I * qmin(1.f, 1.f / length2(dv));  // InverseSquareFalloff
+          Ldir = normalize(p - ld3(lt.position));
+          if (lt.type == QG_LIGHT_SPOT) I = I * spot_attenuation(lt, Ldir);
+        }
+        const V3 L = normalize(-Ldir);
+        const V3 H = normalize(V + L);
+        const float cosNL = qmax(0.f, dot(N, L)), cosNH = qmax(0.f, dot(N, H));
+        contrib = T * ((I * norm_di) * cosNL * (Kd + Ks * powf(cosNH, gloss)));
+        push = (contrib.x != 0.f) || (contrib.y != 0.f) || (contrib.z != 0.f);
+      }
+      const uint32_t mask = __ballot_sync(0xFFFFFFFFu, push);
+      if (mask) {
+        uint32_t qbase = 0;
+        if (lane == 0) qbase = atomicAdd(&B.counters[QB_CNT_SHADOW + d], (uint32_t) __popc(mask));
+        qbase = __shfl_sync(0xFFFFFFFFu, qbase, 0);
+        if (push) {
+          const uint32_t q = qbase + __popc(mask & lt_mask);
+          B.s0[q] = make_float4(p.x, p.y, p.z, sdir.x);
+          B.s1[q] = make_float4(sdir.y, sdir.z, tmax, __int_as_float(slot));
+          B.s2[q] = make_float4(contrib.x, contrib.y, contrib.z, 0.f);
+        }
+      }
+    }
+
+    // ---- queue compaction: surviving paths go to the state buffer of depth d+1
+    const uint32_t amask = __ballot_sync(0xFFFFFFFFu, alive);
+    if (amask) {
+      uint32_t qbase = 0;
+      if (lane == 0) qbase = atomicAdd(&B.counters[QB_CNT_PATHS + d + 1], (uint32_t) __popc(amask));
+      qbase = __shfl_sync(0xFFFFFFFFu, qbase, 0);
+      if (alive) {
+        const uint32_t q = qbase + __popc(amask & lt_mask);
+        const V3 nd = normalize(next_dir);  // DiffRay::Normalize in ComputeSecondaryRay (:235-236)
+        B.ps0[nb][q] = make_float4(p.x, p.y, p.z, nd.x);
+        B.ps1[nb][q] = make_float4(nd.y, nd.z, __int_as_float(slot), __uint_as_float(rng.key));
+        B.ps2[nb][q] = make_float4(next_T.x, next_T.y, next_T.z, __uint_as_float((rng.n << 8) | next_flags));
+        B.ps3[nb][q] = make_float4(next_absorb.x, next_absorb.y, next_absorb.z, 0.f);
+      }
+    }
+  }
+}
+
+// ---- resolve ---------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float linear_to_srgb(float c)  // renderer.cpp:34-39
+{
+  const float a = 0.055f;
+  if (c < 0.0031308f) return 12.92f * c;
+  return (1.f + a) * powf(c, 1.f / 2.4f) - a;
+}
+
+__global__ void k_resolve(const float *__restrict__ accum, const float *__restrict__ depth_in, int n, int spp, int srgb,
+                          float *__restrict__ rgb_mean, uint8_t *__restrict__ rgb8, float *__restrict__ depth_out,
+                          uint8_t *__restrict__ sample_count, uint8_t *__restrict__ mask)
+{
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float4 a = reinterpret_cast<const float4 *>(accum)[i];
+  const float w = a.w;
+  V3 c = w > 0.f ? v3(a.x / w, a.y / w, a.z / w) : v3(0.f);
+  if (rgb_mean) { rgb_mean[3 * i] = c.x; rgb_mean[3 * i + 1] = c.y; rgb_mean[3 * i + 2] = c.z; }
+  if (rgb8) {
+    if (srgb) c = v3(linear_to_srgb(c.x), linear_to_srgb(c.y), linear_to_srgb(c.z));
+    c = v3(qmax(0.f, qmin(1.f, c.x)), qmax(0.f, qmin(1.f, c.y)), qmax(0.f, qmin(1.f, c.z)));
+    rgb8[3 * i + 0] = (uint8_t) roundf(c.x * 255.f);
+    rgb8[3 * i + 1] = (uint8_t) roundf(c.y * 255.f);
+    rgb8[3 * i + 2] = (uint8_t) roundf(c.z * 255.f);
+  }
+  if (depth_out) depth_out[i] = depth_in ? depth_in[i] : 0.f;
+  // sampleCountBuffer = 255 * samples taken / sppMax (renderer.cpp:362-363); mask = pixel rendered (:364)
+  if (sample_count) sample_count[i] = (uint8_t) (255.f * w / (float) spp);
+  if (mask) mask[i] = w > 0.f ? 1 : 0;
+}
+
+// wave epilogue: fold the wave's queue counters into the running ray statistics
+__global__ void k_wf_stats(const uint32_t *__restrict__ counters, unsigned long long *__restrict__ stats, int max_bounce)
+{
+  unsigned long long closest = 0, shadow = 0;
+  for (int d = 0; d <= max_bounce; ++d) {
+    if (d >= 1) closest += counters[QB_CNT_PATHS + d];
+    shadow += counters[QB_CNT_SHADOW + d];
+  }
+  stats[0] += closest;
+  stats[1] += shadow;
+}
+void launch_wf_stats(const WfBuffers &B, int max_bounce, cudaStream_t st) { k_wf_stats<<<1, 1, 0, st>>>(B.counters, B.stats, max_bounce); }
+
+static int persistent_grid_shade()
+{
+  int dev = 0, sms = 0, per_sm = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void *) k_wf_shade, QB_BLOCK, 0);
+  if (per_sm < 1) per_sm = 1;
+  return sms * per_sm;
+}
+int wf_shade_grid() { static int g = persistent_grid_shade(); return g; }
+
+void launch_wf_shade(const DScene &S, const WfBuffers &B, const WfParams &P, int grid, cudaStream_t st)
+{
+  k_wf_shade<<<grid, QB_BLOCK, 0, st>>>(S, B, P);
+}
+void launch_resolve(const float *accum, const float *depth_in, int n, int spp, int srgb, float *rgb_mean, uint8_t *rgb8, float *depth_out,
+                    uint8_t *sample_count, uint8_t *mask, cudaStream_t st)
+{
+  k_resolve<<<(n + 255) / 256, 256, 0, st>>>(accum, depth_in, n, spp, srgb, rgb_mean, rgb8, depth_out, sample_count, mask);
+}
+
+}  // namespace qb

@@ -1,0 +1,428 @@
+// trace.cuh — ray/scene intersection device code. MUST be compiled with --fmad=false: every expression below
+// keeps the reference's operation order so hit/miss, primitive id and t are bit-identical to its CPU code
+// (oracle build: -O2 -ffp-contract=off). Division and sqrt are the IEEE-rounded defaults of nvcc
+// (-prec-div=true -prec-sqrt=true), denormals are kept (-ftz=false).
+//
+//   Scene::TraceNodeNormal / TraceNodeShadow   src/scene/scene.cpp:35-74      -> trace_closest / trace_any
+//   Node::ToNodeCoords / FromNodeCoords        src/core/node.cpp:112-139      -> to_node / from_node
+//   Sphere::IntersectRay                       src/objects/objects.cpp:55-141
+//   Plane::IntersectRay                        src/objects/objects.cpp:149-208
+//   TriObj::IntersectRay + Box::IntersectRay   src/objects/objects.cpp:310-322, src/core/box.cpp:94-128
+//   TriObj::TraceBVHNode                       src/objects/objects.cpp:324-420
+//   TriObj::IntersectTriangle                  src/objects/objects.cpp:212-306
+#pragma once
+#include "dev_scene.h"
+
+namespace qb {
+
+struct Ray3 {
+  V3 p, d;
+};
+
+struct TraceCounters {
+  unsigned long long nodes, tris, objects;
+};
+
+#ifdef QB_COUNT
+#define QB_CNT(field) (cnt.field++)
+#else
+#define QB_CNT(field) ((void) 0)
+#endif
+
+__device__ __forceinline__ V3 xyz(float4 v) { return v3(v.x, v.y, v.z); }
+
+// Node::ToNodeCoords(Ray): p' = itm*(p-pos); dir' = itm*((p+dir)-pos) - p'   (not itm*dir: the rounding differs)
+__device__ __forceinline__ Ray3 to_node(const DNode *__restrict__ n, Ray3 r)
+{
+  const float4 i0 = __ldg(&n->i0), i1 = __ldg(&n->i1), i2 = __ldg(&n->i2);
+  const V3 pos = v3(i0.w, i1.w, i2.w);
+  const V3 a = r.p - pos;
+  const V3 b = (r.p + r.d) - pos;
+  Ray3 o;
+  o.p = v3(i0.x * a.x + i1.x * a.y + i2.x * a.z, i0.y * a.x + i1.y * a.y + i2.y * a.z, i0.z * a.x + i1.z * a.y + i2.z * a.z);
+  const V3 q = v3(i0.x * b.x + i1.x * b.y + i2.x * b.z, i0.y * b.x + i1.y * b.y + i2.y * b.z, i0.z * b.x + i1.z * b.y + i2.z * b.z);
+  o.d = q - o.p;
+  return o;
+}
+
+// Node::FromNodeCoords(HitInfo): p = tm*p + pos; N = normalize(itm^T * N)
+__device__ __forceinline__ void from_node(const DNode *__restrict__ n, V3 &p, V3 &N)
+{
+  const float4 i0 = __ldg(&n->i0), i1 = __ldg(&n->i1), i2 = __ldg(&n->i2);
+  const float4 t0 = __ldg(&n->t0), t1 = __ldg(&n->t1), t2 = __ldg(&n->t2);
+  p = v3(t0.x * p.x + t1.x * p.y + t2.x * p.z, t0.y * p.x + t1.y * p.y + t2.y * p.z, t0.z * p.x + t1.z * p.y + t2.z * p.z) +
+      v3(i0.w, i1.w, i2.w);
+  N = normalize(v3(dot(xyz(i0), N), dot(xyz(i1), N), dot(xyz(i2), N)));
+}
+
+// ray of object k's node space: the root's transform was already applied to r0
+__device__ __forceinline__ Ray3 chain_ray(const DScene &S, int k, Ray3 r0)
+{
+  const int b = __ldg(&S.chain_off[k]), e = __ldg(&S.chain_off[k + 1]);
+  Ray3 r = r0;
+  for (int c = b; c < e; ++c) r = to_node(&S.nodes[__ldg(&S.chain[c])], r);
+  return r;
+}
+
+// ---- analytic objects: return the accepted t (z > t held) or a negative number ------------------------------
+__device__ __forceinline__ float sphere_t(const Ray3 &r, float z)
+{
+  const float a = dot(r.d, r.d);
+  const float b = 2.f * dot(r.p, r.d);
+  const float c = dot(r.p, r.p) - 1;
+  const float rcp2a = 1.f / (2.f * a);
+  const float delta = b * b - 4 * a * c;
+  float t = QB_BIGFLOAT;
+  if (delta < 0) return -1.f;
+  if (delta == 0) {
+    const float t0 = -b * rcp2a;
+    if (t0 <= QB_BIAS) return -1.f;
+    t = t0;
+  } else {
+    const float sd = sqrtf(delta);
+    const float t1 = (-b - sd) * rcp2a;
+    const float t2 = (-b + sd) * rcp2a;
+    if (t1 <= QB_BIAS && t2 <= QB_BIAS) return -1.f;
+    else if (t1 > QB_BIAS) t = qmin(t, t1);
+    else if (t2 > QB_BIAS) t = qmin(t, t2);
+  }
+  return z > t ? t : -1.f;
+}
+
+__device__ __forceinline__ float plane_t(const Ray3 &r, float z)
+{
+  const float dz = r.d.z;  // dot(dir,(0,0,1)) is exactly dir.z for finite dir
+  if (qabs(dz) < 1e-7f) return -1.f;
+  const float t = -r.p.z / dz;
+  if (t <= QB_BIAS) return -1.f;
+  if (!(z > t)) return -1.f;
+  const V3 p = r.p + r.d * t;
+  if (qabs(p.x) > 1.f || qabs(p.y) > 1.f) return -1.f;
+  return t;
+}
+
+// Box::IntersectRay(ray, t_max) for the whole-mesh box (note the non-strict comparisons, unlike the BVH test)
+__device__ __forceinline__ bool mesh_box_hit(const DMesh *__restrict__ m, const Ray3 &r, float t_max)
+{
+  const V3 drcp = v3(1.f, 1.f, 1.f) / r.d;
+  const V3 bmin = v3(__ldg(&m->bmin[0]), __ldg(&m->bmin[1]), __ldg(&m->bmin[2]));
+  const V3 bmax = v3(__ldg(&m->bmax[0]), __ldg(&m->bmax[1]), __ldg(&m->bmax[2]));
+  const V3 p0 = -(r.p - bmin) * drcp;
+  const V3 p1 = -(r.p - bmax) * drcp;
+  float t0x, t1x, t0y, t1y, t0z, t1z;
+  if (qabs(r.d.x) < 1e-7f) { t0x = -QB_BIGFLOAT; t1x = QB_BIGFLOAT; } else { t0x = qmin(p0.x, p1.x); t1x = qmax(p0.x, p1.x); }
+  if (qabs(r.d.y) < 1e-7f) { t0y = -QB_BIGFLOAT; t1y = QB_BIGFLOAT; } else { t0y = qmin(p0.y, p1.y); t1y = qmax(p0.y, p1.y); }
+  if (qabs(r.d.z) < 1e-7f) { t0z = -QB_BIGFLOAT; t1z = QB_BIGFLOAT; } else { t0z = qmin(p0.z, p1.z); t1z = qmax(p0.z, p1.z); }
+  const float entry = qmax(t0x, qmax(t0y, t0z));
+  const float exit = qmin(t1x, qmin(t1y, t1z));
+  return !(entry > t_max || entry > exit);
+}
+
+__device__ __forceinline__ float tri_area(int axis, V3 A, V3 B, V3 C)  // TriangleArea, objects.cpp:30-41
+{
+  if (axis == 0) return (B.y - A.y) * (C.z - A.z) - (C.y - A.y) * (B.z - A.z);
+  if (axis == 1) return (B.x - A.x) * (C.z - A.z) - (C.x - A.x) * (B.z - A.z);
+  return (B.x - A.x) * (C.y - A.y) - (C.x - A.x) * (B.y - A.y);
+}
+__device__ __forceinline__ int tri_axis(V3 N)
+{
+  const float ax = qabs(N.x), ay = qabs(N.y), az = qabs(N.z);
+  if (ax > ay && ax > az) return 0;
+  if (ay > az) return 1;
+  return 2;
+}
+
+// IntersectTriangle up to the acceptance decision. N is the unit face normal the reference recomputes per test,
+// here computed once on the host with the same expression. Returns accepted t or a negative number.
+__device__ __forceinline__ float tri_t(const Ray3 &r, float z, V3 A, V3 B, V3 C, V3 N)
+{
+  const float dz = dot(r.d, N);
+  if (qabs(dz) < 1e-7f) return -1.f;
+  const float pz = dot(r.p - A, N);
+  const float t = -pz / dz;
+  if (t <= QB_BIAS) return -1.f;
+  if (!(z > t)) return -1.f;
+  const V3 p = r.p + t * r.d;
+  const int axis = tri_axis(N);
+  const float s = 1.f / tri_area(axis, A, B, C);
+  const float a = tri_area(axis, p, B, C) * s;
+  const float b = tri_area(axis, p, C, A) * s;
+  const float c = 1.f - a - b;
+  if (a < 0 || b < 0 || c < 0) return -1.f;
+  return t;
+}
+
+// TraceBVHNode. ANY = stop at the first accepted triangle (the reference finishes the traversal, but its
+// return value is the same boolean). Returns the slot of the last accepted triangle (closest) or -1; z updated.
+template <bool ANY>
+__device__ __forceinline__ int bvh_trace(const DScene &S, uint32_t root_ref, const Ray3 &r, float &z, int &uv_slot, float &uv_t,
+                                         TraceCounters &cnt)
+{
+  uint32_t stack[QB_STACK];
+  int sp = 0;
+  stack[sp++] = root_ref;
+  const V3 drcp = v3(1.f, 1.f, 1.f) / r.d;
+  const bool gx = qabs(r.d.x) < 1e-7f, gy = qabs(r.d.y) < 1e-7f, gz = qabs(r.d.z) < 1e-7f;
+  int best = -1;
+  while (sp != 0) {
+    const uint32_t ref = stack[--sp];
+    if (ref & QB_LEAF_BIT) {
+      const uint32_t base = ref & 0x0FFFFFFFu;
+      const uint32_t count = ((ref >> 28) & 7u) + 1u;
+      for (uint32_t i = 0; i < count; ++i) {
+        const DTri *tp = &S.tris[base + i];
+        const float4 ta = __ldg(&tp->a), tb = __ldg(&tp->b), tc = __ldg(&tp->c);
+        QB_CNT(tris);
+        const float t = tri_t(r, z, xyz(ta), xyz(tb), xyz(tc), v3(ta.w, tb.w, tc.w));
+        if (t > 0.f) {
+          z = t;
+          best = (int) (base + i);
+          if (ANY) return best;
+          // remember the last accepted triangle that carries texture coordinates (bit 31 of tri_face)
+          if (__ldg(&S.tri_face[base + i]) & 0x80000000u) { uv_slot = best; uv_t = t; }
+        }
+      }
+    } else {
+      const DBvhNode *np = &S.bvh[ref];
+      const float4 na = __ldg(&np->a), nb = __ldg(&np->b), nc = __ldg(&np->c);
+      const uint4 nd = __ldg(&np->d);
+      QB_CNT(nodes);
+      // p = -(rpos - bound) * drcp, per component; min/max per axis unless the axis is degenerate
+      const float p00x = -(r.p.x - na.x) * drcp.x, p00y = -(r.p.y - na.y) * drcp.y, p00z = -(r.p.z - na.z) * drcp.z;
+      const float p01x = -(r.p.x - na.w) * drcp.x, p01y = -(r.p.y - nb.x) * drcp.y, p01z = -(r.p.z - nb.y) * drcp.z;
+      const float p10x = -(r.p.x - nb.z) * drcp.x, p10y = -(r.p.y - nb.w) * drcp.y, p10z = -(r.p.z - nc.x) * drcp.z;
+      const float p11x = -(r.p.x - nc.y) * drcp.x, p11y = -(r.p.y - nc.z) * drcp.y, p11z = -(r.p.z - nc.w) * drcp.z;
+      const float t00x = gx ? -QB_BIGFLOAT : qmin(p00x, p01x), t01x = gx ? QB_BIGFLOAT : qmax(p00x, p01x);
+      const float t10x = gx ? -QB_BIGFLOAT : qmin(p10x, p11x), t11x = gx ? QB_BIGFLOAT : qmax(p10x, p11x);
+      const float t00y = gy ? -QB_BIGFLOAT : qmin(p00y, p01y), t01y = gy ? QB_BIGFLOAT : qmax(p00y, p01y);
+      const float t10y = gy ? -QB_BIGFLOAT : qmin(p10y, p11y), t11y = gy ? QB_BIGFLOAT : qmax(p10y, p11y);
+      const float t00z = gz ? -QB_BIGFLOAT : qmin(p00z, p01z), t01z = gz ? QB_BIGFLOAT : qmax(p00z, p01z);
+      const float t10z = gz ? -QB_BIGFLOAT : qmin(p10z, p11z), t11z = gz ? QB_BIGFLOAT : qmax(p10z, p11z);
+      const float t_max = z;
+      const float entry0 = qmax(t00x, qmax(t00y, t00z));
+      const float entry1 = qmax(t10x, qmax(t10y, t10z));
+      const float exit0 = qmin(t01x, qmin(t01y, t01z));
+      const float exit1 = qmin(t11x, qmin(t11y, t11z));
+      const bool h0 = (entry0 < t_max && entry0 < exit0);
+      const bool h1 = (entry1 < t_max && entry1 < exit1);
+      if (h0 && h1) {
+        if (entry0 < entry1) { stack[sp++] = nd.y; stack[sp++] = nd.x; }
+        else { stack[sp++] = nd.x; stack[sp++] = nd.y; }
+      } else if (h0) {
+        stack[sp++] = nd.x;
+      } else if (h1) {
+        stack[sp++] = nd.y;
+      }
+    }
+  }
+  return best;
+}
+
+// One object test in Scene::TraceNode* order. Returns true when hInfo would have been updated; slot = triangle slot.
+template <bool ANY>
+__device__ __forceinline__ bool object_test(const DScene &S, const DNode *__restrict__ n, const Ray3 &r, float &z, int &slot,
+                                            int &uv_slot, float &uv_t, TraceCounters &cnt)
+{
+  const int type = __ldg(&n->type);
+  QB_CNT(objects);
+  slot = -1;
+  if (type == QG_OBJ_SPHERE) {
+    const float t = sphere_t(r, z);
+    if (t > 0.f) { z = t; return true; }
+    return false;
+  }
+  if (type == QG_OBJ_PLANE) {
+    const float t = plane_t(r, z);
+    if (t > 0.f) { z = t; return true; }
+    return false;
+  }
+  const DMesh *m = &S.meshes[__ldg(&n->mesh)];
+  if (__ldg(&m->num_faces) == 0u) return false;
+  if (!mesh_box_hit(m, r, z)) return false;
+  slot = bvh_trace<ANY>(S, __ldg(&m->root_ref), r, z, uv_slot, uv_t, cnt);
+  return slot >= 0;
+}
+
+// ---- hit attributes ---------------------------------------------------------------------------------------------
+struct HitAttr {
+  V3 p, N;          // world space after FromNodeCoords up the chain
+  V3 uvw, duvw0, duvw1;
+  int front, has_texture, mtl_id, face;  // face = id inside the mesh, -1 for sphere/plane
+};
+
+__device__ __forceinline__ V3 sphere_uvw(V3 p, float rcp_l)  // Sphere_TexCoord, objects.cpp:48-53
+{
+  const float RCP_PI = 1.f / 3.14159274101257324f, RCP_2PI = 1.f / (2.f * 3.14159274101257324f);
+  return v3(0.5f - atan2f(p.x, p.y) * RCP_2PI, 0.5f + asinf(p.z * rcp_l) * RCP_PI, 0.f);
+}
+__device__ __forceinline__ V3 plane_uvw(V3 p) { return v3((p.x + 1.f) * 0.5f, (p.y + 1.f) * 0.5f, 0.f); }
+
+// The texture part of an accepted hit on object node n (sphere, plane, or triangle WITH uv): what IntersectRay
+// writes into hInfo.uvw / hInfo.duvw. rc/rx/ry are the rays in the node's space. Returns false for a triangle
+// without texture vertices (the reference then leaves uvw/duvw/hasTexture as an earlier hit wrote them).
+__device__ __forceinline__ bool hit_texture(const DScene &S, const DNode *__restrict__ n, int slot, float t, const Ray3 &rc,
+                                            const Ray3 &rx, const Ray3 &ry, bool with_diff, V3 &uvw, V3 &d0, V3 &d1)
+{
+  const float rdx = 1.f / 0.01f;
+  const int type = __ldg(&n->type);
+  d0 = v3(0.f);
+  d1 = v3(0.f);
+  if (type == QG_OBJ_SPHERE) {
+    const V3 p = rc.p + rc.d * t;
+    const V3 N = normalize(p);
+    uvw = sphere_uvw(p, 1.f);
+    if (with_diff) {
+      const float t_x = -dot(rx.p - p, N) / dot(rx.d, N);
+      const float t_y = -dot(ry.p - p, N) / dot(ry.d, N);
+      const V3 p_x = rx.p + rx.d * t_x, p_y = ry.p + ry.d * t_y;
+      d0 = rdx * (sphere_uvw(p_x, 1.f / length(p_x)) - uvw);
+      d1 = rdx * (sphere_uvw(p_y, 1.f / length(p_y)) - uvw);
+    }
+    return true;
+  }
+  if (type == QG_OBJ_PLANE) {
+    const V3 p = rc.p + rc.d * t;
+    uvw = plane_uvw(p);
+    if (with_diff) {
+      const float t_x = -rx.p.z / rx.d.z, t_y = -ry.p.z / ry.d.z;
+      d0 = rdx * (plane_uvw(rx.p + rx.d * t_x) - uvw);
+      d1 = rdx * (plane_uvw(ry.p + ry.d * t_y) - uvw);
+    }
+    return true;
+  }
+  const uint32_t gface = __ldg(&S.tri_face[slot]) & 0x7FFFFFFFu;
+  const DFace *f = &S.faces[gface];
+  if (!(__ldg(&f->mtl_uv) & 1)) return false;
+  const DTri *tp = &S.tris[slot];
+  const float4 ta = __ldg(&tp->a), tb = __ldg(&tp->b), tc = __ldg(&tp->c);
+  const V3 A = xyz(ta), B = xyz(tb), C = xyz(tc), N = v3(ta.w, tb.w, tc.w);
+  const int axis = tri_axis(N);
+  const float s = 1.f / tri_area(axis, A, B, C);
+  const V3 p = rc.p + t * rc.d;
+  const float a = tri_area(axis, p, B, C) * s, b = tri_area(axis, p, C, A) * s, c = 1.f - a - b;
+  const float u0 = __ldg(&f->uv[0]), v0 = __ldg(&f->uv[1]), u1 = __ldg(&f->uv[2]), v1 = __ldg(&f->uv[3]), u2 = __ldg(&f->uv[4]),
+              v2 = __ldg(&f->uv[5]);
+  uvw = v3(u0 * a + u1 * b + u2 * c, v0 * a + v1 * b + v2 * c, 0.f);  // GetTexCoord: VT0*bc.x + VT1*bc.y + VT2*bc.z
+  if (with_diff) {
+    const float t_x = -dot(rx.p - A, N) / dot(rx.d, N);
+    const float t_y = -dot(ry.p - A, N) / dot(ry.d, N);
+    const V3 p_x = rx.p + rx.d * t_x, p_y = ry.p + ry.d * t_y;
+    const float ax = tri_area(axis, p_x, B, C) * s, bx = tri_area(axis, p_x, C, A) * s, cx = 1.f - ax - bx;
+    const float ay = tri_area(axis, p_y, B, C) * s, by = tri_area(axis, p_y, C, A) * s, cy = 1.f - ay - by;
+    d0 = rdx * (v3(u0 * ax + u1 * bx + u2 * cx, v0 * ax + v1 * bx + v2 * cx, 0.f) - uvw);
+    d1 = rdx * (v3(u0 * ay + u1 * by + u2 * cy, v0 * ay + v1 * by + v2 * cy, 0.f) - uvw);
+  }
+  return true;
+}
+
+// Geometric part of the final hit (p, N, front, mtlID, face) in node space, then FromNodeCoords up to the root.
+__device__ __forceinline__ void hit_geometry(const DScene &S, int k, const DNode *__restrict__ n, int slot, float t, const Ray3 &rc,
+                                             HitAttr &h)
+{
+  const int type = __ldg(&n->type);
+  V3 p, N;
+  h.face = -1;
+  h.mtl_id = 0;
+  if (type == QG_OBJ_SPHERE) {
+    p = rc.p + rc.d * t;
+    N = normalize(p);
+    h.front = dot(N, rc.d) <= 0;
+  } else if (type == QG_OBJ_PLANE) {
+    p = rc.p + rc.d * t;
+    N = v3(0.f, 0.f, 1.f);
+    h.front = rc.d.z <= 0;
+  } else {
+    const uint32_t gface = __ldg(&S.tri_face[slot]) & 0x7FFFFFFFu;
+    const DFace *f = &S.faces[gface];
+    const DTri *tp = &S.tris[slot];
+    const float4 ta = __ldg(&tp->a), tb = __ldg(&tp->b), tc = __ldg(&tp->c);
+    const V3 A = xyz(ta), B = xyz(tb), C = xyz(tc), Ng = v3(ta.w, tb.w, tc.w);
+    h.front = dot(rc.d, Ng) <= 0;
+    const int axis = tri_axis(Ng);
+    const float s = 1.f / tri_area(axis, A, B, C);
+    p = rc.p + t * rc.d;
+    const float a = tri_area(axis, p, B, C) * s, b = tri_area(axis, p, C, A) * s, c = 1.f - a - b;
+    // GetNormal: VN0*bc.x + VN1*bc.y + VN2*bc.z, left unnormalised until FromNodeCoords
+    N = v3(__ldg(&f->n[0]) * a + __ldg(&f->n[3]) * b + __ldg(&f->n[6]) * c, __ldg(&f->n[1]) * a + __ldg(&f->n[4]) * b + __ldg(&f->n[7]) * c,
+           __ldg(&f->n[2]) * a + __ldg(&f->n[5]) * b + __ldg(&f->n[8]) * c);
+    h.mtl_id = (__ldg(&f->mtl_uv) >> 1) - 1;
+    h.face = (int) (gface - __ldg(&S.meshes[__ldg(&n->mesh)].face_base));
+  }
+  // FromNodeCoords on the way out: the object node first, then its ancestors, then the root
+  const int b = __ldg(&S.chain_off[k]), e = __ldg(&S.chain_off[k + 1]);
+  for (int c = e - 1; c >= b; --c) from_node(&S.nodes[__ldg(&S.chain[c])], p, N);
+  from_node(&S.nodes[0], p, N);
+  h.p = p;
+  h.N = N;
+}
+
+// ---- Scene::TraceNodeNormal -------------------------------------------------------------------------------------
+// c/x/y: world-space rays; with_diff=false treats x and y as absent (duvw = 0), the form used for secondary rays.
+// stale_tex: reproduce the reference's carry-over of uvw/duvw/hasTexture from an earlier, farther hit when the
+// closest hit is a triangle without texture coordinates (IntersectTriangle leaves those fields untouched).
+// Returns the object index (into obj_node) or -1; z = hit distance.
+__device__ __forceinline__ int trace_closest(const DScene &S, const Ray3 &c, const Ray3 &x, const Ray3 &y, bool with_diff,
+                                             bool stale_tex, float &z, HitAttr &h, TraceCounters &cnt)
+{
+  const DNode *root = &S.nodes[0];
+  const Ray3 c0 = to_node(root, c);
+  z = QB_BIGFLOAT;
+  int best_k = -1, best_slot = -1;
+  int tex_k = -1, tex_slot = -1;
+  float tex_t = 0.f;
+  for (int k = 0; k < S.num_obj; ++k) {
+    const DNode *n = &S.nodes[__ldg(&S.obj_node[k])];
+    const Ray3 r = chain_ray(S, k, c0);
+    int slot, uv_slot = -1;
+    float uv_t = 0.f;
+    if (object_test<false>(S, n, r, z, slot, uv_slot, uv_t, cnt)) {
+      best_k = k;
+      best_slot = slot;
+      if (slot < 0) { tex_k = k; tex_slot = -1; tex_t = z; }                    // sphere / plane always write uvw
+      else if (uv_slot >= 0) { tex_k = k; tex_slot = uv_slot; tex_t = uv_t; }   // last accepted triangle with uv
+    }
+  }
+  if (best_k < 0) return -1;
+  const DNode *n = &S.nodes[__ldg(&S.obj_node[best_k])];
+  const Ray3 r = chain_ray(S, best_k, c0);
+  hit_geometry(S, best_k, n, best_slot, z, r, h);
+  h.uvw = v3(0.5f, 0.5f, 0.5f);
+  h.duvw0 = v3(0.f);
+  h.duvw1 = v3(0.f);
+  h.has_texture = 0;
+  if (tex_k == best_k && tex_slot == best_slot) {
+    Ray3 rx = r, ry = r;
+    if (with_diff) {
+      rx = chain_ray(S, best_k, to_node(root, x));
+      ry = chain_ray(S, best_k, to_node(root, y));
+    }
+    h.has_texture = hit_texture(S, n, best_slot, z, r, rx, ry, with_diff, h.uvw, h.duvw0, h.duvw1) ? 1 : 0;
+  } else if (tex_k >= 0 && stale_tex) {
+    const DNode *tn = &S.nodes[__ldg(&S.obj_node[tex_k])];
+    const Ray3 tr = chain_ray(S, tex_k, c0);
+    Ray3 rx = tr, ry = tr;
+    if (with_diff) {
+      rx = chain_ray(S, tex_k, to_node(root, x));
+      ry = chain_ray(S, tex_k, to_node(root, y));
+    }
+    h.has_texture = hit_texture(S, tn, tex_slot, tex_t, tr, rx, ry, with_diff, h.uvw, h.duvw0, h.duvw1) ? 1 : 0;
+  }
+  return best_k;
+}
+
+// ---- Scene::TraceNodeShadow: any hit with bias < t < tmax ------------------------------------------------------
+__device__ __forceinline__ bool trace_any(const DScene &S, const Ray3 &c, float tmax, TraceCounters &cnt)
+{
+  const Ray3 c0 = to_node(&S.nodes[0], c);
+  float z = tmax;
+  for (int k = 0; k < S.num_obj; ++k) {
+    const DNode *n = &S.nodes[__ldg(&S.obj_node[k])];
+    const Ray3 r = chain_ray(S, k, c0);
+    int slot, uv_slot;
+    float uv_t;
+    if (object_test<true>(S, n, r, z, slot, uv_slot, uv_t, cnt)) return true;
+  }
+  return false;
+}
+
+}  // namespace qb

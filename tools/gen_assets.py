@@ -372,9 +372,12 @@ def cornell(n):
     short = box([130, 0, 65], [295, 165, 230], max(1, n // 2))
     tall = box([265, 0, 295], [430, 330, 460], max(1, n // 2))
     light = box([213, 548.0, 227], [343, 548.7, 332], 1)
-    return merge([room, Mesh(short.v, short.f, short.vt, np.zeros(len(short.f), np.int64)),
-                  Mesh(tall.v, tall.f, tall.vt, np.zeros(len(tall.f), np.int64)),
-                  Mesh(light.v, light.f, light.vt, np.full(len(light.f), 3, np.int64))], None), None
+    parts = [room, Mesh(short.v, short.f, short.vt, np.zeros(len(short.f), np.int64)),
+             Mesh(tall.v, tall.f, tall.vt, np.zeros(len(tall.f), np.int64)),
+             Mesh(light.v, light.f, light.vt, np.full(len(light.f), 3, np.int64))]
+    m = merge(parts, None)
+    m.mtl = np.concatenate([p.mtl for p in parts])   # per-face material ids survive the merge (usemtl lines)
+    return m, None
 
 
 # ------------------------------------------------------------------------------------------ textures
