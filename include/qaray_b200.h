@@ -156,6 +156,7 @@ typedef struct qgRenderStats {
   uint64_t kernel_launches;
   uint64_t nodes_visited, tris_tested, objects_tested; /* filled by the counting build only, else 0 */
   double device_ms;       /* CUDA-event time of the render on its stream */
+  double trace_ms, shade_ms, shadow_ms; /* summed launch durations per kernel class (closest-hit, shade, any-hit) */
 } qgRenderStats;
 
 typedef struct qgSceneInfo {

@@ -97,8 +97,10 @@ struct qgScene {
   uint32_t wf_capacity = 0;
   DevBuf<unsigned long long> stats;
   cudaStream_t stream = nullptr;
+  std::vector<cudaEvent_t> ev_pool;  // timestamp events of KernelClock
   ~qgScene()
   {
+    for (cudaEvent_t e : ev_pool) cudaEventDestroy(e);
     for (void *p : wf_allocs) cudaFree(p);
     if (stream) cudaStreamDestroy(stream);
   }
@@ -454,23 +456,58 @@ int make_params(const qgScene *sc, const qgRenderParams *rp, WfParams *P, Shard 
   return QG_OK;
 }
 
+// Per-kernel-class device time: one timestamp event after every launch (class = 0 trace, 1 shade, 2 shadow,
+// 3 other); a launch's duration is the gap to the previous timestamp on the same stream. Events come from a pool
+// owned by the scene so a render creates none after its first call.
+struct KernelClock {
+  qgScene *sc;
+  cudaStream_t st;
+  bool on;
+  size_t used = 0;
+  std::vector<int> cls;
+  void stamp(int c)
+  {
+    if (!on) return;
+    if (used == sc->ev_pool.size()) {
+      cudaEvent_t e;
+      if (cudaEventCreate(&e) != cudaSuccess) { on = false; return; }
+      sc->ev_pool.push_back(e);
+    }
+    cudaEventRecord(sc->ev_pool[used++], st);
+    cls.push_back(c);
+  }
+  void sums(double out[4]) const
+  {
+    for (int k = 0; k < 4; ++k) out[k] = 0.0;
+    for (size_t i = 1; i < used; ++i) {
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, sc->ev_pool[i - 1], sc->ev_pool[i]) == cudaSuccess) out[cls[i]] += ms;
+    }
+  }
+};
+
 // one wave: depth loop of trace -> shade -> shadow, all on `st`, no host synchronisation
-void run_wave(qgScene *sc, WfParams P, cudaStream_t st, uint64_t *launches)
+void run_wave(qgScene *sc, WfParams P, cudaStream_t st, uint64_t *launches, KernelClock *clk = nullptr)
 {
   const WfBuffers &B = sc->wf;
   cudaMemsetAsync(B.counters, 0, QB_CNT_WORDS * sizeof(uint32_t), st);
+  if (clk) clk->stamp(3);
   const int gt = wf_trace_grid(), gs = wf_shade_grid(), gsh = wf_shadow_grid();
   for (int d = 0; d <= P.max_bounce; ++d) {
     P.depth = d;
     launch_wf_trace(sc->dev, B, P, gt, st);
+    if (clk) clk->stamp(0);
     launch_wf_shade(sc->dev, B, P, gs, st);
+    if (clk) clk->stamp(1);
     *launches += 2;
     if (sc->dev.num_nonambient > 0) {
       launch_wf_shadow(sc->dev, B, P, gsh, st);
+      if (clk) clk->stamp(2);
       *launches += 1;
     }
   }
   launch_wf_stats(B, P.max_bounce, st);
+  if (clk) clk->stamp(3);
   *launches += 1;
 }
 
@@ -493,10 +530,11 @@ int render_accumulate(qgScene *sc, const qgRenderParams *rp, float *d_accum, flo
   CU(cudaMemsetAsync(sc->stats.p, 0, sc->stats.bytes(), st));
   CU(cudaEventRecord(e0, st));
   uint64_t launches = 0;
+  KernelClock clk{sc, st, stats != nullptr};
   for (unsigned long long base = 0; base < sh.total_paths; base += cap) {
     P.wave_base = base;
     P.n_paths = (uint32_t) std::min<unsigned long long>(cap, sh.total_paths - base);
-    run_wave(sc, P, st, &launches);
+    run_wave(sc, P, st, &launches, &clk);
   }
   CU(cudaEventRecord(e1, st));
   CU(cudaStreamSynchronize(st));
@@ -515,6 +553,11 @@ int render_accumulate(qgScene *sc, const qgRenderParams *rp, float *d_accum, flo
     stats->objects_tested = hs[4];
     stats->kernel_launches = launches;
     stats->device_ms = ms;
+    double cms[4];
+    clk.sums(cms);
+    stats->trace_ms = cms[0];
+    stats->shade_ms = cms[1];
+    stats->shadow_ms = cms[2];
   }
   cudaEventDestroy(e0);
   cudaEventDestroy(e1);

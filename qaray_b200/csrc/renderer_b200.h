@@ -1,0 +1,124 @@
+// renderer_b200.h — C++ host side of the drop-in boundary: the reference's renderer interface
+// (RendererParam, Renderer::Init / ComputeScene / Render / Terminate; src/renderers/renderer.h:47-110, driven from
+// src/main.cpp:46-59) over the C ABI of include/qaray_b200.h. Header-only; links against libqaray_b200.so.
+// Everything that computes happens behind qg_*: there is no CPU path here.
+//
+// Error behaviour follows the reference: LoadScene returns 0/1 and prints (src/parser/xmlload.cpp:71-95); the
+// other calls print the library's message and return false instead of throwing (the reference uses no exceptions).
+#pragma once
+#include <cstdio>
+#include <cstdlib>
+#include <string>
+#include <vector>
+
+#include "../../include/qaray_b200.h"
+
+namespace qaray_b200 {
+
+// RendererParam (renderer.h:47-68). The photon-map switches are accepted and refused at Render time: the photon
+// pass is outside this path ("next" row 3).
+struct RendererParam {
+  bool useSRGB = true;
+  size_t sppMax = 8;
+  size_t sppMin = 4;
+  bool usePhotonMap = false;
+  size_t photonMapSize = 10000, causticsMapSize = 1000;
+  int maxBounce = 5;  // Material::maxBounce (src/core/material.cpp:31)
+  unsigned seed = 0x5EEDu;
+  int width = 0, height = 0;  // 0 = the XML camera's
+  void SetPhotonMappingFlag(bool f) { usePhotonMap = f; }
+  void SetPhotonMapSize(size_t s) { photonMapSize = s; }
+  void SetCausticsMapSize(size_t s) { causticsMapSize = s; }
+  void SetSPPMax(int spp) { sppMax = (size_t) spp; }
+  void SetSPPMin(int spp) { sppMin = (size_t) spp; }
+  void SetSRGBFlag(bool f) { useSRGB = f; }
+};
+
+class Renderer_B200 {
+ protected:
+  RendererParam &param;
+  qgScene *scene = nullptr;
+  std::string assetDir;
+  size_t pixelW = 0, pixelH = 0;
+  size_t mpiSize = 1, mpiRank = 0;  // Renderer::mpiSize / mpiRank: the interleaved 4x4-tile shard (renderer.cpp:383-387)
+ public:
+  std::vector<uint8_t> colorBuffer, sampleCountBuffer, maskBuffer;  // FrameBuffer planes (src/fb/framebuffer.h:35-95)
+  std::vector<float> depthBuffer, linearBuffer;
+  qgRenderStats stats{};
+
+  explicit Renderer_B200(RendererParam &p) : param(p) {}
+  ~Renderer_B200() { Terminate(); }
+  void SetShard(size_t rank, size_t size) { mpiRank = rank; mpiSize = size; }
+  void SetAssetDir(const std::string &d) { assetDir = d; }
+  size_t W() const { return pixelW; }
+  size_t H() const { return pixelH; }
+
+  bool Init(int device = 0)
+  {
+    if (qg_init(device) != QG_OK) { fprintf(stderr, "Renderer_B200::Init: %s\n", qg_last_error()); return false; }
+    return true;
+  }
+  // LoadScene(filename): 1 on success, 0 on failure
+  int LoadScene(const char *filename)
+  {
+    if (scene) { qg_scene_destroy(scene); scene = nullptr; }
+    if (qg_scene_load_xml(filename, assetDir.c_str(), &scene) != QG_OK) {
+      printf("Failed to load the file \"%s\": %s\n", filename, qg_last_error());
+      return 0;
+    }
+    return 1;
+  }
+  // Renderer::ComputeScene: image size and plane allocation (the camera frame itself is computed by the library)
+  bool ComputeScene()
+  {
+    qgSceneInfo info;
+    if (!scene || qg_scene_info(scene, &info) != QG_OK) return false;
+    pixelW = (size_t) (param.width > 0 ? param.width : info.camera.width);
+    pixelH = (size_t) (param.height > 0 ? param.height : info.camera.height);
+    const size_t n = pixelW * pixelH;
+    colorBuffer.assign(3 * n, 0);
+    depthBuffer.assign(n, 0.f);
+    sampleCountBuffer.assign(n, 0);
+    maskBuffer.assign(n, 0);
+    linearBuffer.assign(3 * n, 0.f);
+    return true;
+  }
+  // Renderer::Render (batch): ThreadRender over this shard's tiles; fills the planes PixelRender fills
+  bool Render()
+  {
+    if (param.usePhotonMap) { fprintf(stderr, "Renderer_B200: -use-photon-map is not on the GPU path\n"); return false; }
+    if (param.sppMin != param.sppMax) {
+      fprintf(stderr, "Renderer_B200: adaptive sampling (sppMin != sppMax) is not on the GPU path; use -spp N\n");
+      return false;
+    }
+    qgRenderParams rp{};
+    rp.spp = (int32_t) param.sppMax;
+    rp.max_bounce = param.maxBounce;
+    rp.srgb = param.useSRGB ? 1 : 0;
+    rp.seed = param.seed;
+    rp.width = (int32_t) pixelW;
+    rp.height = (int32_t) pixelH;
+    rp.tile_rank = (int32_t) mpiRank;
+    rp.tile_ranks = (int32_t) mpiSize;
+    if (qg_render(scene, &rp, linearBuffer.data(), colorBuffer.data(), depthBuffer.data(), sampleCountBuffer.data(), maskBuffer.data(),
+                  &stats) != QG_OK) {
+      fprintf(stderr, "Renderer_B200::Render: %s\n", qg_last_error());
+      return false;
+    }
+    return true;
+  }
+  // the PNG set of Renderer_MPI::Render (src/renderers/Renderer_MPI.cpp:134-138)
+  bool SaveImages(const std::string &prefix = "")
+  {
+    const int w = (int) pixelW, h = (int) pixelH;
+    return qg_save_png_rgb8((prefix + "colorBuffer.png").c_str(), colorBuffer.data(), w, h) == QG_OK &&
+           qg_save_png_depth((prefix + "depthBuffer.png").c_str(), depthBuffer.data(), w, h) == QG_OK &&
+           qg_save_png_gray8((prefix + "sampleBuffer.png").c_str(), sampleCountBuffer.data(), w, h) == QG_OK;
+  }
+  void Terminate()
+  {
+    if (scene) { qg_scene_destroy(scene); scene = nullptr; }
+  }
+};
+
+}  // namespace qaray_b200
