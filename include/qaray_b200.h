@@ -154,7 +154,8 @@ typedef struct qgRenderStats {
   uint64_t closest_rays;  /* Scene::TraceNodeNormal calls on the root */
   uint64_t shadow_rays;   /* Scene::TraceNodeShadow calls on the root */
   uint64_t kernel_launches;
-  uint64_t nodes_visited, tris_tested, objects_tested; /* filled by the counting build only, else 0 */
+  uint64_t nodes_visited, tris_tested, objects_tested; /* closest-hit rays; filled by the counting build only, else 0 */
+  uint64_t shadow_nodes_visited, shadow_tris_tested, shadow_objects_tested; /* same for any-hit rays */
   double device_ms;       /* CUDA-event time of the render on its stream */
   double trace_ms, shade_ms, shadow_ms; /* summed launch durations per kernel class (closest-hit, shade, any-hit) */
 } qgRenderStats;

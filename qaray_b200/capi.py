@@ -77,7 +77,8 @@ class RenderParams(C.Structure):
 
 class RenderStats(C.Structure):
     _fields_ = [("samples", u64), ("closest_rays", u64), ("shadow_rays", u64), ("kernel_launches", u64),
-                ("nodes_visited", u64), ("tris_tested", u64), ("objects_tested", u64), ("device_ms", C.c_double),
+                ("nodes_visited", u64), ("tris_tested", u64), ("objects_tested", u64), ("shadow_nodes_visited", u64), ("shadow_tris_tested", u64),
+                ("shadow_objects_tested", u64), ("device_ms", C.c_double),
                 ("trace_ms", C.c_double), ("shade_ms", C.c_double), ("shadow_ms", C.c_double)]
 
 

@@ -551,6 +551,9 @@ int render_accumulate(qgScene *sc, const qgRenderParams *rp, float *d_accum, flo
     stats->nodes_visited = hs[2];
     stats->tris_tested = hs[3];
     stats->objects_tested = hs[4];
+    stats->shadow_nodes_visited = hs[5];
+    stats->shadow_tris_tested = hs[6];
+    stats->shadow_objects_tested = hs[7];
     stats->kernel_launches = launches;
     stats->device_ms = ms;
     double cms[4];

@@ -368,7 +368,7 @@ __device__ __forceinline__ int trace_closest(const DScene &S, const Ray3 &c, con
   const Ray3 c0 = to_node(root, c);
   z = QB_BIGFLOAT;
   int best_k = -1, best_slot = -1;
-  int tex_k = -1, tex_slot = -1;
+  int tex_k = -1, tex_slot = -1, last_tri = -1;
   float tex_t = 0.f;
   for (int k = 0; k < S.num_obj; ++k) {
     const DNode *n = &S.nodes[__ldg(&S.obj_node[k])];
@@ -378,6 +378,7 @@ __device__ __forceinline__ int trace_closest(const DScene &S, const Ray3 &c, con
     if (object_test<false>(S, n, r, z, slot, uv_slot, uv_t, cnt)) {
       best_k = k;
       best_slot = slot;
+      if (slot >= 0) last_tri = slot;
       if (slot < 0) { tex_k = k; tex_slot = -1; tex_t = z; }                    // sphere / plane always write uvw
       else if (uv_slot >= 0) { tex_k = k; tex_slot = uv_slot; tex_t = uv_t; }   // last accepted triangle with uv
     }
@@ -386,6 +387,9 @@ __device__ __forceinline__ int trace_closest(const DScene &S, const Ray3 &c, con
   const DNode *n = &S.nodes[__ldg(&S.obj_node[best_k])];
   const Ray3 r = chain_ray(S, best_k, c0);
   hit_geometry(S, best_k, n, best_slot, z, r, h);
+  // Sphere/Plane::IntersectRay never write hInfo.mtlID: it keeps what an earlier, farther triangle hit left there
+  if (best_slot < 0 && last_tri >= 0 && stale_tex)
+    h.mtl_id = (__ldg(&S.faces[__ldg(&S.tri_face[last_tri]) & 0x7FFFFFFFu].mtl_uv) >> 1) - 1;
   h.uvw = v3(0.5f, 0.5f, 0.5f);
   h.duvw0 = v3(0.f);
   h.duvw1 = v3(0.f);

@@ -10,6 +10,7 @@
 // long rays do not hold back a statically assigned tail and no host sync is needed between bounces.
 #include "trace.cuh"
 #include "wavefront.h"
+#include <algorithm>
 
 namespace qb {
 
@@ -29,19 +30,24 @@ __device__ __forceinline__ void primary_ray(const WfParams &P, int i, int j, int
   y.d = normalize(ypt - P.cam_pos);
 }
 
-__device__ __forceinline__ void flush_counters(unsigned long long *stats, const TraceCounters &cnt)
+// counting build only: stats[2..4] = BVH nodes / triangles / objects visited by closest-hit rays, [5..7] by any-hit rays
+__device__ __forceinline__ void flush_counters(unsigned long long *stats, const TraceCounters &cnt, int base = 2)
 {
 #ifdef QB_COUNT
-  atomicAdd(&stats[2], cnt.nodes);
-  atomicAdd(&stats[3], cnt.tris);
-  atomicAdd(&stats[4], cnt.objects);
+  atomicAdd(&stats[base + 0], cnt.nodes);
+  atomicAdd(&stats[base + 1], cnt.tris);
+  atomicAdd(&stats[base + 2], cnt.objects);
 #endif
 }
 
+// PRIMARY = depth 0 (rays generated in registers) / depth >= 1 (rays read from the path state). Two instantiations
+// rather than a run-time branch: with both ray sources in one kernel nvcc 12.9 merged the two definitions of the
+// origin's x component into the camera's (the state load of .x was dropped), found by the radiance parity test.
+template <bool PRIMARY>
 __global__ void __launch_bounds__(QB_BLOCK) k_wf_trace(const DScene S, const WfBuffers B, const WfParams P)
 {
   const int d = P.depth;
-  const uint32_t n = d == 0 ? P.n_paths : B.counters[QB_CNT_PATHS + d];
+  const uint32_t n = PRIMARY ? P.n_paths : B.counters[QB_CNT_PATHS + d];
   const int lane = threadIdx.x & 31;
   const int pb = d & 1;
   TraceCounters cnt = {0, 0, 0};
@@ -53,15 +59,14 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_trace(const DScene S, const WfB
     const uint32_t idx = base + lane;
     if (idx >= n) continue;
     Ray3 c, x, y;
-    bool with_diff = false;
-    if (d == 0) {
+    const bool with_diff = PRIMARY;
+    if (PRIMARY) {
       int i, j, s, slot;
       if (!wf_decode(P, idx, i, j, s, slot)) {
         B.h0[idx] = f4(QB_BIGFLOAT, __int_as_float(-2), 0.f, 0.f);  // padding lane of an edge tile
         continue;
       }
       primary_ray(P, i, j, s, c, x, y);
-      with_diff = true;
     } else {
       const float4 a = B.ps0[pb][idx], b = B.ps1[pb][idx];
       c.p = v3(a.x, a.y, a.z);
@@ -110,7 +115,7 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shadow(const DScene S, const Wf
       atomicAdd(acc + 2, c.z);
     }
   }
-  flush_counters(B.stats, cnt);
+  flush_counters(B.stats, cnt, 5);
 }
 
 // ---- C-ABI ray-buffer kernels -------------------------------------------------------------------------------------
@@ -171,7 +176,7 @@ __global__ void __launch_bounds__(QB_BLOCK) k_trace_any_rays(const DScene S, con
     r.d = v3(rays6[6 * idx + 3], rays6[6 * idx + 4], rays6[6 * idx + 5]);
     occ[idx] = trace_any(S, r, tmax[idx], cnt) ? 1 : 0;
   }
-  flush_counters(stats, cnt);
+  flush_counters(stats, cnt, 5);
 }
 
 __global__ void k_primary_rays(const WfParams P, size_t n, qgRay *__restrict__ out)
@@ -198,12 +203,17 @@ static int persistent_grid(const void *kernel)
   if (per_sm < 1) per_sm = 1;
   return sms * per_sm;
 }
-int wf_trace_grid() { static int g = persistent_grid((const void *) k_wf_trace); return g; }
+int wf_trace_grid()
+{
+  static int g = std::min(persistent_grid((const void *) k_wf_trace<true>), persistent_grid((const void *) k_wf_trace<false>));
+  return g;
+}
 int wf_shadow_grid() { static int g = persistent_grid((const void *) k_wf_shadow); return g; }
 
 void launch_wf_trace(const DScene &S, const WfBuffers &B, const WfParams &P, int grid, cudaStream_t st)
 {
-  k_wf_trace<<<grid, QB_BLOCK, 0, st>>>(S, B, P);
+  if (P.depth == 0) k_wf_trace<true><<<grid, QB_BLOCK, 0, st>>>(S, B, P);
+  else k_wf_trace<false><<<grid, QB_BLOCK, 0, st>>>(S, B, P);
 }
 void launch_wf_shadow(const DScene &S, const WfBuffers &B, const WfParams &P, int grid, cudaStream_t st)
 {
