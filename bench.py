@@ -1,0 +1,387 @@
+#!/usr/bin/env python3
+"""bench.py — throughput of the per-pixel Monte-Carlo loop (BASELINE.json metric: Mrays/s, samples/s) on B200.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--scene NAME] [--spp S]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P bench.py --gpus N ...
+
+A STEP = one render of the workload scene at S samples per pixel PER GPU (bounce 5, sRGB on), i.e. one pass of the
+hot path Renderer::ThreadRender -> PixelRender over the whole frame. With N GPUs every rank renders sample indices
+[rank*S, (rank+1)*S) of an N*S-spp image into a full-frame fp32 {sum R, sum G, sum B, weight} buffer (weak scaling:
+per-GPU work fixed), one NCCL reduce to rank 0 combines the buffers (the path's only exchange step, replacing the
+MPI_Send/Recv gather of src/renderers/Renderer_MPI.cpp:142-207), and rank 0 resolves.
+A RAY = one Scene::TraceNodeNormal or Scene::TraceNodeShadow call on the root node.
+
+value   device-timed whole-job Mrays/s with the scene resident in HBM (CUDA events on the launching stream, max over
+        ranks), accumulate + reduce only.
+e2e     the same metric through the C ABI with HOST output buffers: qg_render (N=1) or accumulate/reduce/qg_resolve
+        (N>1), frame planes copied device->host inside the timed region.
+roofline  for the dominant kernel class (closest-hit or any-hit traversal): algorithmic bytes per the formula of
+        SURVEY.md 8(d), counted by the -DQB_COUNT build of the same kernels, over the class's summed launch time.
+cpu_baseline / --impl reference   the reference's own CPU renderer (oracle/_ref/qaref_perf = its sources compiled
+        by oracle/Makefile, OpenMP tile loop) on this box's host cores, on a bounded spp sample of the same scene.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+REF_INPUTS = os.path.join(ROOT, "oracle", "_ref", "inputs")
+REF_PERF = os.path.join(ROOT, "oracle", "_ref", "qaref_perf")
+ASSETS = os.path.join(ROOT, "assets")
+METRIC = "Mrays/s"
+BOUNCE = 5
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--scene", default="trc_scene_tower")  # the scene BASELINE.json's target is quoted on
+    ap.add_argument("--spp", type=int, default=64, help="samples per pixel per GPU per step")
+    ap.add_argument("--width", type=int, default=0)
+    ap.add_argument("--height", type=int, default=0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target length of the bounded CPU sample")
+    return ap.parse_args()
+
+
+def workload(args):
+    return {"workload": "inputs/%s.xml (stand-in geometry from tools/gen_assets.py), %d spp/GPU/step, bounce %d, sRGB" % (
+        args.scene, args.spp, BOUNCE), "scene": args.scene, "spp_per_gpu": args.spp, "max_bounce": BOUNCE}
+
+
+# ------------------------------------------------------------------------------------------------- clocks
+class ClockSampler(object):
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = str(gpu_index)
+        self.lines = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "200",
+                                          "-i", self.gpu], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thr = threading.Thread(target=self._read, daemon=True)
+            self.thr.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, smax, power, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.lines:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); smax.append(float(f[2])); power.append(float(f[3]))
+            except ValueError:
+                continue
+            for k, nm in enumerate(names):
+                if f[5 + k].lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------------- CPU reference
+def ref_available():
+    return os.path.exists(REF_PERF) and os.path.exists(os.path.join(REF_INPUTS, "example_project3_sphere.xml"))
+
+
+def ref_rays_per_sample(scene, spp=2):
+    """closest + shadow rays per sample counted by the reference itself (oracle/_ref/libqaref_parity.so carries ray
+    counters in Scene::TraceNode*, oracle/Makefile patch P3); stable to ~0.1 % across runs and spp."""
+    code = ("import sys; sys.path.insert(0, %r)\nfrom oracle import refapi\nr = refapi.Ref(); r.set_params(%d, %d, %d, True, 0)\n"
+            "r.load(%r, %r); r.counters(True); r.render(); c, s = r.counters(True); print('RAYS', c, s, r.W * r.H * %d)\n") % (
+        ROOT, spp, spp, BOUNCE, os.path.join(REF_INPUTS, scene + ".xml"), ASSETS, spp)
+    out = subprocess.run([sys.executable, "-c", code], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, timeout=900).stdout
+    for line in out.splitlines():
+        if line.startswith("RAYS"):
+            _, c, s, n = line.split()
+            return (int(c) + int(s)) / float(n), int(c) / float(n), int(s) / float(n)
+    raise RuntimeError("reference ray counting failed: %s" % out[-500:])
+
+
+def ref_perf_run(scene, spp, repeat, threads=0):
+    """the reference's own ThreadRender (its OpenMP tile loop, -O2 -march build) -> seconds per repeat"""
+    cmd = [REF_PERF, os.path.join(REF_INPUTS, scene + ".xml"), ASSETS, str(spp), str(BOUNCE), str(threads), str(repeat)]
+    out = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, timeout=3600).stdout
+    recs = [json.loads(l) for l in out.splitlines() if l.startswith("{")]
+    if len(recs) != repeat:
+        raise RuntimeError("qaref_perf failed: %s" % out[-500:])
+    return recs
+
+
+def cpu_baseline(scene, target_seconds):
+    """bounded sample: calibrate at 1 spp, then one run sized for about target_seconds"""
+    rps, _, _ = ref_rays_per_sample(scene)
+    cal = ref_perf_run(scene, 1, 1)[0]
+    spp = int(max(1, min(256, round(target_seconds / max(cal["seconds"], 1e-3)))))
+    rec = ref_perf_run(scene, spp, 1)[0]
+    mrays = rec["samples"] * rps / rec["seconds"] * 1e-6
+    return {"value": mrays, "unit": METRIC, "cores": rec["threads"], "kind": "reference",
+            "sample": "%s at %dx%d, %d spp, bounce %d: %.2f s on %d OpenMP threads (reference's own ThreadRender, "
+                      "oracle/_ref/qaref_perf); %.3f rays/sample counted by the reference" % (
+                          scene, rec["width"], rec["height"], spp, BOUNCE, rec["seconds"], rec["threads"], rps),
+            "samples_per_s": rec["samples"] / rec["seconds"], "rays_per_sample": rps}
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    if not ref_available():
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref not built (needs /root/reference at build time)"}))
+        return 0
+    rps, _, _ = ref_rays_per_sample(args.scene)
+    cal = ref_perf_run(args.scene, 1, 1)[0]
+    total = max(1, args.steps + args.warmup)
+    spp = int(max(1, min(args.spp, round(150.0 / total / max(cal["seconds"], 1e-3)))))  # whole run within a few minutes
+    recs = ref_perf_run(args.scene, spp, total)[args.warmup:]
+    secs = sum(r["seconds"] for r in recs)
+    samples = sum(r["samples"] for r in recs)
+    val = samples * rps / secs * 1e-6
+    cfg = workload(args)
+    cfg["reference_sample_spp"] = spp
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": METRIC, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": secs / len(recs) * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
+            "samples_per_s": samples / secs,
+            "cpu_baseline": {"value": val, "unit": METRIC, "cores": recs[0]["threads"], "kind": "reference",
+                             "sample": "%d spp per step (bounded sample of the %d spp workload), %.3f rays/sample" % (spp, args.spp, rps)},
+            "e2e": {"value": val, "unit": METRIC, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+    return 0
+
+
+# ------------------------------------------------------------------------------------------------- B200 arm
+def algorithmic_bytes(closest, shadow, cst):
+    """bytes(ray) = 32 (ray in) + 16 (hit out; 1 for any-hit) + 64 * BVH nodes visited + 48 * triangles
+    tested + 48 * instance transforms applied (one per object test). cst = counting-build totals."""
+    per_c = 32 + 16 + (64.0 * cst["nodes"] + 48.0 * cst["tris"] + 48.0 * cst["objects"]) / max(1, cst["closest_rays"])
+    per_s = 32 + 1 + (64.0 * cst["s_nodes"] + 48.0 * cst["s_tris"] + 48.0 * cst["s_objects"]) / max(1, cst["shadow_rays"])
+    return per_c * closest, per_s * shadow, per_c, per_s
+
+
+def run_b200_arm(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from qaray_b200 import capi
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; qaray_b200 has no CPU path (use --impl reference for the CPU baseline)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    lib = capi.load()
+    capi.check(lib, lib.qg_init(local))
+    xml = os.path.join(REF_INPUTS, args.scene + ".xml")
+    t_load = time.time()
+    h = C.c_void_p()
+    capi.check(lib, lib.qg_scene_load_xml(os.fsencode(xml), os.fsencode(ASSETS), C.byref(h)))
+    t_load = time.time() - t_load
+    info = capi.SceneInfo()
+    capi.check(lib, lib.qg_scene_info(h, C.byref(info)))
+    W = args.width or info.camera.width
+    H = args.height or info.camera.height
+    npix = W * H
+    spp_total = args.spp * world
+
+    def params(s0, s1, spp=spp_total):
+        return capi.RenderParams(spp, BOUNCE, 1, 0x5EED, W, H, 0, 1, s0, s1, 0, 0)
+
+    accum = torch.zeros(npix * 4, dtype=torch.float32, device=dev)
+    depth = torch.zeros(npix, dtype=torch.float32, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    stream = torch.cuda.current_stream()
+    sptr = C.c_void_p(stream.cuda_stream)
+    my = params(rank * args.spp, (rank + 1) * args.spp)
+    # host output planes (pinned) for the e2e path
+    pin = lambda *shape, dt=torch.uint8: torch.empty(*shape, dtype=dt).pin_memory()
+    h_mean, h_rgb8, h_depth = pin(npix * 3, dt=torch.float32), pin(npix * 3), pin(npix, dt=torch.float32)
+    h_sc, h_mask = pin(npix), pin(npix)
+    hp = lambda t: C.c_void_p(t.data_ptr())
+    d2h_bytes = npix * (12 + 3 + 4 + 1 + 1)
+    st = capi.RenderStats()
+    tot = {"closest": 0, "shadow": 0, "samples": 0, "launches": 0, "trace_ms": 0.0, "shade_ms": 0.0, "shadow_ms": 0.0, "device_ms": 0.0}
+
+    def step(e2e, count):
+        flush.zero_()  # L2 flush between steps
+        if e2e and world == 1:
+            capi.check(lib, lib.qg_render(h, C.byref(my), hp(h_mean), hp(h_rgb8), hp(h_depth), hp(h_sc), hp(h_mask), C.byref(st)))
+        else:
+            accum.zero_()
+            depth.zero_()
+            capi.check(lib, lib.qg_render_accumulate(h, C.byref(my), C.c_void_p(accum.data_ptr()), C.c_void_p(depth.data_ptr()), sptr,
+                                                     C.byref(st)))
+            if world > 1:
+                dist.reduce(accum, 0)
+                dist.reduce(depth, 0)  # only the shard owning sample 0 wrote depth: sum with zeros
+            if e2e and rank == 0:
+                capi.check(lib, lib.qg_resolve(h, C.byref(my), C.c_void_p(accum.data_ptr()), C.c_void_p(depth.data_ptr()), hp(h_mean),
+                                               hp(h_rgb8), hp(h_depth), hp(h_sc), hp(h_mask), sptr))
+        if count:
+            tot["closest"] += st.closest_rays; tot["shadow"] += st.shadow_rays; tot["samples"] += st.samples
+            tot["launches"] += st.kernel_launches + (1 if e2e and rank == 0 else 0)
+            tot["trace_ms"] += st.trace_ms; tot["shade_ms"] += st.shade_ms; tot["shadow_ms"] += st.shadow_ms
+            tot["device_ms"] += st.device_ms
+
+    def timed(e2e, steps, sample_clocks):
+        for k in tot:
+            tot[k] = 0
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        clk = ClockSampler(local) if sample_clocks else None
+        if clk:
+            clk.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.time()
+        e0.record(stream)
+        for _ in range(steps):
+            step(e2e, True)
+        e1.record(stream)
+        torch.cuda.synchronize()
+        wall = time.time() - t0
+        if world > 1:
+            dist.barrier()
+        clocks = clk.stop() if clk else None
+        ms = e0.elapsed_time(e1)
+        if e2e:
+            ms = max(ms, wall * 1e3)  # host-side work (allocation, copies, waits) counts end to end
+        v = torch.tensor([ms, float(tot["closest"] + tot["shadow"]), float(tot["samples"]), float(tot["launches"])], dtype=torch.float64, device=dev)
+        if world > 1:
+            mx = v.clone()
+            dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+            dist.all_reduce(v, op=dist.ReduceOp.SUM)
+            v[0] = mx[0]
+        return {"ms": float(v[0]), "rays": float(v[1]), "samples": float(v[2]), "launches": int(v[3]), "clocks": clocks, "tot": dict(tot)}
+
+    for _ in range(max(args.warmup, 3)):
+        step(False, False)
+    dev_run = timed(False, args.steps, True)
+    step(True, False)
+    e2e_run = timed(True, args.steps, False)
+    return finish_b200(args, locals())
+
+
+def finish_b200(args, L):
+    """roofline (counting build), CPU baseline and the JSON line; rank 0 prints"""
+    import torch
+    import torch.distributed as dist
+    from qaray_b200 import capi
+    rank, world, lib, h = L["rank"], L["world"], L["lib"], L["h"]
+    dev_run, e2e_run, info = L["dev_run"], L["e2e_run"], L["info"]
+    out = None
+    if rank == 0:
+        # per-ray node / triangle / object-test counts from the -DQB_COUNT build of the same kernels, 4 spp of the same frame
+        libc = capi.load(counting=True)
+        capi.check(libc, libc.qg_init(L["local"]))
+        hc = C.c_void_p()
+        capi.check(libc, libc.qg_scene_load_xml(os.fsencode(L["xml"]), os.fsencode(ASSETS), C.byref(hc)))
+        pc = capi.RenderParams(4, BOUNCE, 1, 0x5EED, L["W"], L["H"], 0, 1, 0, 0, 0, 0)
+        sc = capi.RenderStats()
+        acc = torch.zeros(L["npix"] * 4, dtype=torch.float32, device=L["dev"])
+        capi.check(libc, libc.qg_render_accumulate(hc, C.byref(pc), C.c_void_p(acc.data_ptr()), None, L["sptr"], C.byref(sc)))
+        libc.qg_scene_destroy(hc)
+        cst = {"closest_rays": sc.closest_rays, "shadow_rays": sc.shadow_rays, "nodes": sc.nodes_visited, "tris": sc.tris_tested,
+               "objects": sc.objects_tested, "s_nodes": sc.shadow_nodes_visited, "s_tris": sc.shadow_tris_tested,
+               "s_objects": sc.shadow_objects_tested}
+        t = dev_run["tot"]  # rank 0's own totals over the timed steps
+        bytes_c, bytes_s, per_c, per_s = algorithmic_bytes(t["closest"], t["shadow"], cst)
+        if t["trace_ms"] >= t["shadow_ms"]:
+            kname, kbytes, kms, klaunch = "k_wf_trace (closest-hit traversal)", bytes_c, t["trace_ms"], per_c
+        else:
+            kname, kbytes, kms, klaunch = "k_wf_shadow (any-hit traversal)", bytes_s, t["shadow_ms"], per_s
+        peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+        if os.path.exists(peaks_path):
+            peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
+        else:
+            peak, peak_src = 6650.0, "B200_PROFILING.md fallback (of fallback)"
+        n_launch = max(1, (BOUNCE + 1) * args.steps * max(1, -(-int(t["samples"] / args.steps * 16 / 16) // (1 << 21))))
+        achieved = kbytes / (kms * 1e-3) * 1e-9 if kms > 0 else 0.0
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "traffic.json")  # dram bytes per launch from the ncu --set full capture, if recorded
+        if os.path.exists(tp):
+            traffic = json.load(open(tp)).get(kname.split(" ")[0])
+        roofline = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                    "traffic": traffic, "peak_source": peak_src, "bytes_per_ray": klaunch, "kernel_ms_per_step": kms / args.steps,
+                    "launches_of_kernel": n_launch,
+                    "per_ray": {"closest": {"nodes": cst["nodes"] / max(1, cst["closest_rays"]), "tris": cst["tris"] / max(1, cst["closest_rays"]),
+                                            "objects": cst["objects"] / max(1, cst["closest_rays"]), "bytes": per_c},
+                                "shadow": {"nodes": cst["s_nodes"] / max(1, cst["shadow_rays"]), "tris": cst["s_tris"] / max(1, cst["shadow_rays"]),
+                                           "objects": cst["s_objects"] / max(1, cst["shadow_rays"]), "bytes": per_s}},
+                    "class_ms_per_step": {"trace": t["trace_ms"] / args.steps, "shade": t["shade_ms"] / args.steps,
+                                          "shadow": t["shadow_ms"] / args.steps, "render_total": t["device_ms"] / args.steps}}
+        value = dev_run["rays"] / (dev_run["ms"] * 1e-3) * 1e-6
+        e2e_v = e2e_run["rays"] / (e2e_run["ms"] * 1e-3) * 1e-6
+        cfg = workload(args)
+        cfg.update({"width": L["W"], "height": L["H"], "spp_total": L["spp_total"], "parallelism": "sample-shard x%d + NCCL reduce" % world if world > 1 else "1 GPU",
+                    "l2": "256 MiB device memset between steps (inside the timed region, ~0.1 ms); path-state working set also exceeds L2",
+                    "triangles": int(info.num_faces), "bvh_nodes": int(info.num_bvh_nodes), "scene_device_bytes": int(info.device_bytes),
+                    "scene_load_s": L["t_load"], "rays_per_sample": dev_run["rays"] / max(1.0, dev_run["samples"])})
+        out = {"metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+               "ms_per_step": dev_run["ms"] / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+               "dtype": "f32", "data": "synthetic", "config": cfg,
+               "samples_per_s": dev_run["samples"] / (dev_run["ms"] * 1e-3),
+               "samples_per_s_per_gpu": dev_run["samples"] / (dev_run["ms"] * 1e-3) / world,
+               "clocks": dev_run["clocks"], "gpu_launches": dev_run["launches"],
+               "e2e": {"value": e2e_v, "unit": METRIC, "h2d_bytes_per_step": C.sizeof(capi.RenderParams),
+                       "d2h_bytes_per_step": L["d2h_bytes"], "ms_per_step": e2e_run["ms"] / args.steps,
+                       "note": "scene resident (uploaded once by qg_scene_load_xml, as the reference loads its scene before Render); "
+                               "per-step input is the parameter block; output = rgb_mean f32 + rgb8 + depth f32 + sampleCount + mask"},
+               "roofline": roofline}
+        if world == 1 and not args.no_cpu_baseline and ref_available():
+            try:
+                out["cpu_baseline"] = cpu_baseline(args.scene, args.cpu_seconds)
+            except Exception as e:  # the baseline is reported, never required for the GPU number
+                out["cpu_baseline"] = {"value": None, "unit": METRIC, "cores": 0, "kind": "reference", "sample": "failed: %s" % e}
+        print(json.dumps(out))
+    lib.qg_scene_destroy(h)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return run_reference_arm(args)
+    return run_b200_arm(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

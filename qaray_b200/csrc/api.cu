@@ -90,7 +90,7 @@ struct qgScene {
   DevBuf<DTexture> textures;
   DevBuf<uchar4> texels;
   int64_t num_faces = 0, num_bvh = 0, device_bytes = 0;
-  int num_obj = 0;
+  int num_obj = 0, max_bvh_depth = 0;
   // wavefront buffers (allocated on first render, sized by capacity)
   WfBuffers wf;
   std::vector<void *> wf_allocs;
@@ -224,6 +224,19 @@ int upload_scene(qgScene *sc)
         if (n.leaf()) return QB_LEAF_BIT | ((n.count() - 1) << 28) | (tri_base + n.offset());
         return internal_index[id];
       };
+      // depth of the tree = most far children a ray can have deferred at once (the shared-memory stack of traverse.cuh)
+      {
+        std::vector<std::pair<uint32_t, int>> todo{{1u, 0}};
+        int max_depth = 0;
+        while (!todo.empty()) {
+          const auto [id, dep] = todo.back();
+          todo.pop_back();
+          max_depth = std::max(max_depth, dep);
+          if (!cy.nodes[id].leaf()) { todo.push_back({cy.nodes[id].child(), dep + 1}); todo.push_back({cy.nodes[id].child() + 1, dep + 1}); }
+        }
+        if (max_depth >= QB_STACK) return fail(QG_EINVAL, "mesh BVH deeper than the traversal stack (QB_STACK)");
+        sc->max_bvh_depth = std::max(sc->max_bvh_depth, max_depth);
+      }
       bvh.resize(bvh_base + ni);
       for (size_t id = 1; id < cy.nodes.size(); ++id) {
         const CyBvh::Node &n = cy.nodes[id];
@@ -517,7 +530,14 @@ int render_accumulate(qgScene *sc, const qgRenderParams *rp, float *d_accum, flo
   Shard sh;
   int rc = make_params(sc, rp, &P, &sh);
   if (rc) return rc;
-  uint32_t cap = rp->batch_paths > 0 ? (uint32_t) rp->batch_paths : (1u << 21);
+  // Paths per wave. Every launch ends with a latency-bound tail (its longest ray walks its BVH nodes one dependent
+  // load after another), so waves are made as large as a fixed slice of HBM allows: 16 GiB of path, hit and
+  // shadow-queue state (12 + 3 * lights float4 per path), at most 2^26 paths.
+  uint32_t cap = (uint32_t) rp->batch_paths;
+  if (rp->batch_paths <= 0) {
+    const unsigned long long per_path = 16ull * (12ull + 3ull * (unsigned long long) std::max(1, sc->dev.num_nonambient));
+    cap = (uint32_t) std::min<unsigned long long>(1ull << 26, (16ull << 30) / per_path);
+  }
   cap = (cap + 31u) & ~31u;
   if ((unsigned long long) cap > sh.total_paths) cap = (uint32_t) std::max<unsigned long long>(32ull, (sh.total_paths + 31ull) & ~31ull);
   rc = ensure_wf(sc, cap);

@@ -18,7 +18,8 @@ namespace qb {
 #define QB_BIGFLOAT 1.0e30f
 #define QB_BIAS 0.005f
 #define QB_MAX_DEPTH 8      // scene-tree depth supported by the chain replay
-#define QB_STACK 64         // BVH stack entries per ray (the reference uses 40, src/objects/objects.cpp:331)
+#define QB_BLOCK 128        // threads per block of every persistent kernel
+#define QB_STACK 48         // deferred far children per ray = max BVH depth supported (the reference keeps 40 entries, objects.cpp:331)
 
 struct DNode {
   float4 i0, i1, i2;  // itm column k in xyz, pos[k] in w      (ToNodeCoords)

@@ -8,7 +8,7 @@
 //
 // Persistent kernels: grid = SMs x resident blocks; each warp pulls 32 consecutive rays from a device cursor, so
 // long rays do not hold back a statically assigned tail and no host sync is needed between bounces.
-#include "trace.cuh"
+#include "traverse.cuh"
 #include "wavefront.h"
 #include <algorithm>
 
@@ -40,116 +40,209 @@ __device__ __forceinline__ void flush_counters(unsigned long long *stats, const 
 #endif
 }
 
-// PRIMARY = depth 0 (rays generated in registers) / depth >= 1 (rays read from the path state). Two instantiations
-// rather than a run-time branch: with both ray sources in one kernel nvcc 12.9 merged the two definitions of the
-// origin's x component into the camera's (the state load of .x was dropped), found by the radiance parity test.
-template <bool PRIMARY>
-__global__ void __launch_bounds__(QB_BLOCK) k_wf_trace(const DScene S, const WfBuffers B, const WfParams P)
+// ---- IO policies of traverse_pool ------------------------------------------------------------------------------------
+// compact hit record of the wavefront: r0 = z, k, slot, tex_slot ; r1 = tex_t, tex_k, last_tri, -
+__device__ __forceinline__ void put_rec(float4 *r0, float4 *r1, uint32_t idx, const HitRec &h)
 {
-  const int d = P.depth;
-  const uint32_t n = PRIMARY ? P.n_paths : B.counters[QB_CNT_PATHS + d];
-  const int lane = threadIdx.x & 31;
-  const int pb = d & 1;
-  TraceCounters cnt = {0, 0, 0};
-  for (;;) {
-    uint32_t base = 0;
-    if (lane == 0) base = atomicAdd(&B.counters[QB_CNT_FETCH_TRACE + d], 32u);
-    base = __shfl_sync(0xFFFFFFFFu, base, 0);
-    if (base >= n) break;
-    const uint32_t idx = base + lane;
-    if (idx >= n) continue;
-    Ray3 c, x, y;
-    const bool with_diff = PRIMARY;
+  r0[idx] = f4(h.z, __int_as_float(h.k), __int_as_float(h.slot), __int_as_float(h.tex_slot));
+  r1[idx] = f4(h.tex_t, __int_as_float(h.tex_k), __int_as_float(h.last_tri), 0.f);
+}
+__device__ __forceinline__ HitRec get_rec(const float4 *r0, const float4 *r1, uint32_t idx)
+{
+  const float4 a = r0[idx], b = r1[idx];
+  HitRec h;
+  h.z = a.x; h.k = __float_as_int(a.y); h.slot = __float_as_int(a.z); h.tex_slot = __float_as_int(a.w);
+  h.tex_t = b.x; h.tex_k = __float_as_int(b.y); h.last_tri = __float_as_int(b.z);
+  return h;
+}
+
+template <bool PRIMARY>
+struct WfClosestIO {
+  const WfBuffers &B;
+  const WfParams &P;
+  uint32_t n;
+  __device__ uint32_t count() const { return n; }
+  __device__ uint32_t *cursor() { return &B.counters[QB_CNT_FETCH_TRACE + P.depth]; }
+  __device__ bool load(uint32_t idx, Ray3 &c, float &tmax)
+  {
+    tmax = QB_BIGFLOAT;
     if (PRIMARY) {
       int i, j, s, slot;
       if (!wf_decode(P, idx, i, j, s, slot)) {
         B.h0[idx] = f4(QB_BIGFLOAT, __int_as_float(-2), 0.f, 0.f);  // padding lane of an edge tile
-        continue;
+        return false;
       }
+      Ray3 x, y;
       primary_ray(P, i, j, s, c, x, y);
     } else {
-      const float4 a = B.ps0[pb][idx], b = B.ps1[pb][idx];
+      const float4 a = B.ps0[P.depth & 1][idx], b = B.ps1[P.depth & 1][idx];
+      c.p = v3(a.x, a.y, a.z);
+      c.d = v3(a.w, b.x, b.y);
+    }
+    return true;
+  }
+  __device__ void store(uint32_t idx, const HitRec &h) { put_rec(B.h1, B.h2, idx, h); }  // h1/h2 double as the record until finish
+  __device__ void store_any(uint32_t, bool) {}
+};
+
+struct WfShadowIO {
+  const WfBuffers &B;
+  const WfParams &P;
+  uint32_t n;
+  __device__ uint32_t count() const { return n; }
+  __device__ uint32_t *cursor() { return &B.counters[QB_CNT_FETCH_SHADOW + P.depth]; }
+  __device__ bool load(uint32_t idx, Ray3 &c, float &tmax)
+  {
+    const float4 a = B.s0[idx], b = B.s1[idx];
+    c.p = v3(a.x, a.y, a.z);
+    c.d = v3(a.w, b.x, b.y);
+    tmax = b.z;
+    return true;
+  }
+  __device__ void store(uint32_t, const HitRec &) {}
+  __device__ void store_any(uint32_t idx, bool occluded)
+  {
+    if (occluded) return;
+    const float4 c = B.s2[idx];
+    float *acc = P.accum + 4ll * (long long) __float_as_int(B.s1[idx].w);
+    atomicAdd(acc + 0, c.x);
+    atomicAdd(acc + 1, c.y);
+    atomicAdd(acc + 2, c.z);
+  }
+};
+
+// PRIMARY = depth 0 (rays generated in registers) / depth >= 1 (rays read from the path state): two instantiations.
+template <bool PRIMARY>
+__global__ void __launch_bounds__(QB_BLOCK) k_wf_trace(const DScene S, const WfBuffers B, const WfParams P)
+{
+  __shared__ uint32_t s_stack[QB_STACK * QB_BLOCK];
+  TraceCounters cnt = {0, 0, 0};
+  WfClosestIO<PRIMARY> io{B, P, PRIMARY ? P.n_paths : B.counters[QB_CNT_PATHS + P.depth]};
+  traverse_pool<false>(S, io, s_stack, cnt);
+  flush_counters(B.stats, cnt);
+}
+
+// hit attributes of the wave's rays from the compact records, one thread per ray (full warps): h0..h3 for shade
+template <bool PRIMARY>
+__global__ void __launch_bounds__(QB_BLOCK) k_wf_finish(const DScene S, const WfBuffers B, const WfParams P)
+{
+  const uint32_t n = PRIMARY ? P.n_paths : B.counters[QB_CNT_PATHS + P.depth];
+  for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += gridDim.x * blockDim.x) {
+    Ray3 c, x, y;
+    if (PRIMARY) {
+      int i, j, s, slot;
+      if (!wf_decode(P, idx, i, j, s, slot)) continue;  // h0 already marks the padding lane
+      primary_ray(P, i, j, s, c, x, y);
+    } else {
+      const float4 a = B.ps0[P.depth & 1][idx], b = B.ps1[P.depth & 1][idx];
       c.p = v3(a.x, a.y, a.z);
       c.d = v3(a.w, b.x, b.y);
       x = c;
       y = c;
     }
-    float z;
-    HitAttr h;
-    const int k = trace_closest(S, c, x, y, with_diff, P.stale_tex != 0, z, h, cnt);
-    if (k < 0) {
+    const HitRec rec = get_rec(B.h1, B.h2, idx);
+    if (rec.k < 0) {
       B.h0[idx] = f4(QB_BIGFLOAT, __int_as_float(-1), 0.f, 0.f);
-    } else {
-      const int flags = (h.front ? 1 : 0) | (h.has_texture ? 2 : 0);
-      B.h0[idx] = f4(z, __int_as_float(S.obj_node[k]), __int_as_float(h.mtl_id), __int_as_float(flags));
-      B.h1[idx] = f4(h.p.x, h.p.y, h.p.z, h.N.x);
-      B.h2[idx] = f4(h.N.y, h.N.z, h.uvw.x, h.uvw.y);
-      B.h3[idx] = f4(h.duvw0.x, h.duvw0.y, h.duvw1.x, h.duvw1.y);
+      continue;
     }
+    HitAttr h;
+    finish_hit(S, rec, c, x, y, PRIMARY, P.stale_tex != 0, h);
+    const int flags = (h.front ? 1 : 0) | (h.has_texture ? 2 : 0);
+    B.h0[idx] = f4(rec.z, __int_as_float(S.obj_node[rec.k]), __int_as_float(h.mtl_id), __int_as_float(flags));
+    B.h1[idx] = f4(h.p.x, h.p.y, h.p.z, h.N.x);
+    B.h2[idx] = f4(h.N.y, h.N.z, h.uvw.x, h.uvw.y);
+    B.h3[idx] = f4(h.duvw0.x, h.duvw0.y, h.duvw1.x, h.duvw1.y);
   }
-  flush_counters(B.stats, cnt);
 }
 
 __global__ void __launch_bounds__(QB_BLOCK) k_wf_shadow(const DScene S, const WfBuffers B, const WfParams P)
 {
-  const int d = P.depth;
-  const uint32_t n = B.counters[QB_CNT_SHADOW + d];
-  const int lane = threadIdx.x & 31;
+  __shared__ uint32_t s_stack[QB_STACK * QB_BLOCK];
   TraceCounters cnt = {0, 0, 0};
-  for (;;) {
-    uint32_t base = 0;
-    if (lane == 0) base = atomicAdd(&B.counters[QB_CNT_FETCH_SHADOW + d], 32u);
-    base = __shfl_sync(0xFFFFFFFFu, base, 0);
-    if (base >= n) break;
-    const uint32_t idx = base + lane;
-    if (idx >= n) continue;
-    const float4 a = B.s0[idx], b = B.s1[idx];
-    Ray3 r;
-    r.p = v3(a.x, a.y, a.z);
-    r.d = v3(a.w, b.x, b.y);
-    if (!trace_any(S, r, b.z, cnt)) {
-      const float4 c = B.s2[idx];
-      float *acc = P.accum + 4ll * (long long) __float_as_int(b.w);
-      atomicAdd(acc + 0, c.x);
-      atomicAdd(acc + 1, c.y);
-      atomicAdd(acc + 2, c.z);
-    }
-  }
+  WfShadowIO io{B, P, B.counters[QB_CNT_SHADOW + P.depth]};
+  traverse_pool<true>(S, io, s_stack, cnt);
   flush_counters(B.stats, cnt, 5);
 }
 
-// ---- C-ABI ray-buffer kernels -------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(QB_BLOCK) k_trace_closest_rays(const DScene S, const qgRay *__restrict__ rays, size_t n,
-                                                                 qgHit *__restrict__ out, unsigned long long *stats)
+// ---- C-ABI ray-buffer kernels: the same traversal core over caller-supplied rays ----------------------------------------
+__device__ __forceinline__ void unpack_ray(const qgRay &q, Ray3 &c, Ray3 &x, Ray3 &y)
 {
+  c.p = v3(q.p[0], q.p[1], q.p[2]);
+  c.d = v3(q.dir[0], q.dir[1], q.dir[2]);
+  if (q.has_diff) {
+    x.p = v3(q.xp[0], q.xp[1], q.xp[2]);
+    x.d = v3(q.xdir[0], q.xdir[1], q.xdir[2]);
+    y.p = v3(q.yp[0], q.yp[1], q.yp[2]);
+    y.d = v3(q.ydir[0], q.ydir[1], q.ydir[2]);
+  } else {
+    x = c;  // DiffRay(p, d): x and y are copies of the centre ray (src/core/ray.h:51-56)
+    y = c;
+  }
+}
+
+struct RayBufClosestIO {
+  const qgRay *rays;
+  uint32_t n;
+  uint32_t *cur;
+  float4 *r0, *r1;
+  __device__ uint32_t count() const { return n; }
+  __device__ uint32_t *cursor() { return cur; }
+  __device__ bool load(uint32_t idx, Ray3 &c, float &tmax)
+  {
+    tmax = QB_BIGFLOAT;
+    c.p = v3(rays[idx].p[0], rays[idx].p[1], rays[idx].p[2]);
+    c.d = v3(rays[idx].dir[0], rays[idx].dir[1], rays[idx].dir[2]);
+    return true;
+  }
+  __device__ void store(uint32_t idx, const HitRec &h) { put_rec(r0, r1, idx, h); }
+  __device__ void store_any(uint32_t, bool) {}
+};
+
+struct RayBufAnyIO {
+  const float *rays6, *tmaxs;
+  uint32_t n;
+  uint32_t *cur;
+  uint8_t *occ;
+  __device__ uint32_t count() const { return n; }
+  __device__ uint32_t *cursor() { return cur; }
+  __device__ bool load(uint32_t idx, Ray3 &c, float &tmax)
+  {
+    c.p = v3(rays6[6 * idx + 0], rays6[6 * idx + 1], rays6[6 * idx + 2]);
+    c.d = v3(rays6[6 * idx + 3], rays6[6 * idx + 4], rays6[6 * idx + 5]);
+    tmax = tmaxs[idx];
+    return true;
+  }
+  __device__ void store(uint32_t, const HitRec &) {}
+  __device__ void store_any(uint32_t idx, bool occluded) { occ[idx] = occluded ? 1 : 0; }
+};
+
+__global__ void __launch_bounds__(QB_BLOCK) k_trace_closest_rays(const DScene S, RayBufClosestIO io, unsigned long long *stats)
+{
+  __shared__ uint32_t s_stack[QB_STACK * QB_BLOCK];
   TraceCounters cnt = {0, 0, 0};
-  for (size_t idx = (size_t) blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += (size_t) gridDim.x * blockDim.x) {
-    const qgRay q = rays[idx];
+  traverse_pool<false>(S, io, s_stack, cnt);
+  flush_counters(stats, cnt);
+}
+
+__global__ void __launch_bounds__(QB_BLOCK) k_finish_rays(const DScene S, const qgRay *__restrict__ rays, uint32_t n, const float4 *r0,
+                                                          const float4 *r1, qgHit *__restrict__ out)
+{
+  for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += gridDim.x * blockDim.x) {
     Ray3 c, x, y;
-    c.p = v3(q.p[0], q.p[1], q.p[2]);
-    c.d = v3(q.dir[0], q.dir[1], q.dir[2]);
-    if (q.has_diff) {
-      x.p = v3(q.xp[0], q.xp[1], q.xp[2]);
-      x.d = v3(q.xdir[0], q.xdir[1], q.xdir[2]);
-      y.p = v3(q.yp[0], q.yp[1], q.yp[2]);
-      y.d = v3(q.ydir[0], q.ydir[1], q.ydir[2]);
-    } else {
-      x = c;  // DiffRay(p, d): x and y are copies of the centre ray (src/core/ray.h:51-56)
-      y = c;
-    }
-    float z;
-    HitAttr h;
-    // objects always see hasDiffRay = true (Node::ToNodeCoords returns a default-constructed DiffRay), so the
-    // differential branch runs for every ray
-    const int k = trace_closest(S, c, x, y, true, true, z, h, cnt);
+    unpack_ray(rays[idx], c, x, y);
+    const HitRec rec = get_rec(r0, r1, idx);
     qgHit o;
     memset(&o, 0, sizeof o);
-    o.hit = k >= 0;
+    o.hit = rec.k >= 0;
     o.node = -1;
     o.face = -1;
-    o.z = z;
-    if (k >= 0) {
-      o.node = S.obj_node[k];
+    o.z = rec.z;
+    if (rec.k >= 0) {
+      HitAttr h;
+      // objects always see hasDiffRay = true (Node::ToNodeCoords returns a default-constructed DiffRay), so the
+      // differential branch runs for every ray
+      finish_hit(S, rec, c, x, y, true, true, h);
+      o.node = S.obj_node[rec.k];
       o.face = h.face;
       o.mtl_id = h.mtl_id;
       o.front = h.front;
@@ -162,20 +255,13 @@ __global__ void __launch_bounds__(QB_BLOCK) k_trace_closest_rays(const DScene S,
     }
     out[idx] = o;
   }
-  flush_counters(stats, cnt);
 }
 
-__global__ void __launch_bounds__(QB_BLOCK) k_trace_any_rays(const DScene S, const float *__restrict__ rays6,
-                                                             const float *__restrict__ tmax, size_t n, uint8_t *__restrict__ occ,
-                                                             unsigned long long *stats)
+__global__ void __launch_bounds__(QB_BLOCK) k_trace_any_rays(const DScene S, RayBufAnyIO io, unsigned long long *stats)
 {
+  __shared__ uint32_t s_stack[QB_STACK * QB_BLOCK];
   TraceCounters cnt = {0, 0, 0};
-  for (size_t idx = (size_t) blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += (size_t) gridDim.x * blockDim.x) {
-    Ray3 r;
-    r.p = v3(rays6[6 * idx + 0], rays6[6 * idx + 1], rays6[6 * idx + 2]);
-    r.d = v3(rays6[6 * idx + 3], rays6[6 * idx + 4], rays6[6 * idx + 5]);
-    occ[idx] = trace_any(S, r, tmax[idx], cnt) ? 1 : 0;
-  }
+  traverse_pool<true>(S, io, s_stack, cnt);
   flush_counters(stats, cnt, 5);
 }
 
@@ -212,8 +298,15 @@ int wf_shadow_grid() { static int g = persistent_grid((const void *) k_wf_shadow
 
 void launch_wf_trace(const DScene &S, const WfBuffers &B, const WfParams &P, int grid, cudaStream_t st)
 {
-  if (P.depth == 0) k_wf_trace<true><<<grid, QB_BLOCK, 0, st>>>(S, B, P);
-  else k_wf_trace<false><<<grid, QB_BLOCK, 0, st>>>(S, B, P);
+  // traversal by the lane pool, then the hit attributes by full warps
+  const int fg = 148 * 8;
+  if (P.depth == 0) {
+    k_wf_trace<true><<<grid, QB_BLOCK, 0, st>>>(S, B, P);
+    k_wf_finish<true><<<fg, QB_BLOCK, 0, st>>>(S, B, P);
+  } else {
+    k_wf_trace<false><<<grid, QB_BLOCK, 0, st>>>(S, B, P);
+    k_wf_finish<false><<<fg, QB_BLOCK, 0, st>>>(S, B, P);
+  }
 }
 void launch_wf_shadow(const DScene &S, const WfBuffers &B, const WfParams &P, int grid, cudaStream_t st)
 {
@@ -222,18 +315,29 @@ void launch_wf_shadow(const DScene &S, const WfBuffers &B, const WfParams &P, in
 static int flat_grid(size_t n)
 {
   size_t g = (n + QB_BLOCK - 1) / QB_BLOCK;
-  if (g > 148 * 16) g = 148 * 16;
+  if (g > 148 * 8) g = 148 * 8;
   if (g < 1) g = 1;
   return (int) g;
 }
-void launch_trace_closest_rays(const DScene &S, const qgRay *rays, size_t n, qgHit *out, unsigned long long *stats, cudaStream_t st)
+// scratch: 1 + 8 * n words (work cursor, then two float4 records per ray), zero the cursor before the call
+size_t trace_rays_scratch_bytes(size_t n) { return 16 + 32 * n; }
+void launch_trace_closest_rays(const DScene &S, const qgRay *rays, size_t n, qgHit *out, unsigned long long *stats, void *scratch,
+                               cudaStream_t st)
 {
-  k_trace_closest_rays<<<flat_grid(n), QB_BLOCK, 0, st>>>(S, rays, n, out, stats);
+  uint32_t *cur = (uint32_t *) scratch;
+  float4 *r0 = (float4 *) ((char *) scratch + 16), *r1 = r0 + n;
+  cudaMemsetAsync(cur, 0, 16, st);
+  RayBufClosestIO io{rays, (uint32_t) n, cur, r0, r1};
+  k_trace_closest_rays<<<flat_grid(n), QB_BLOCK, 0, st>>>(S, io, stats);
+  k_finish_rays<<<flat_grid(n), QB_BLOCK, 0, st>>>(S, rays, (uint32_t) n, r0, r1, out);
 }
 void launch_trace_any_rays(const DScene &S, const float *rays6, const float *tmax, size_t n, uint8_t *occ, unsigned long long *stats,
-                           cudaStream_t st)
+                           void *scratch, cudaStream_t st)
 {
-  k_trace_any_rays<<<flat_grid(n), QB_BLOCK, 0, st>>>(S, rays6, tmax, n, occ, stats);
+  uint32_t *cur = (uint32_t *) scratch;
+  cudaMemsetAsync(cur, 0, 16, st);
+  RayBufAnyIO io{rays6, tmax, (uint32_t) n, cur, occ};
+  k_trace_any_rays<<<flat_grid(n), QB_BLOCK, 0, st>>>(S, io, stats);
 }
 void launch_primary_rays(const WfParams &P, size_t n, qgRay *out, cudaStream_t st)
 {

@@ -98,15 +98,16 @@ void launch_wf_shade(const DScene &S, const WfBuffers &B, const WfParams &P, int
 void launch_wf_stats(const WfBuffers &B, int max_bounce, cudaStream_t st);
 void launch_resolve(const float *accum, const float *depth_in, int n, int spp, int srgb, float *rgb_mean, uint8_t *rgb8, float *depth_out,
                     uint8_t *sample_count, uint8_t *mask, cudaStream_t st);
-void launch_trace_closest_rays(const DScene &S, const qgRay *rays, size_t n, qgHit *out, unsigned long long *stats, cudaStream_t st);
+size_t trace_rays_scratch_bytes(size_t n);  // device scratch the two ray-buffer launchers need
+void launch_trace_closest_rays(const DScene &S, const qgRay *rays, size_t n, qgHit *out, unsigned long long *stats, void *scratch,
+                               cudaStream_t st);
 void launch_trace_any_rays(const DScene &S, const float *rays6, const float *tmax, size_t n, uint8_t *occ, unsigned long long *stats,
-                           cudaStream_t st);
+                           void *scratch, cudaStream_t st);
 void launch_primary_rays(const WfParams &P, size_t n, qgRay *out, cudaStream_t st);
 int wf_trace_grid();   // persistent grid sizes (blocks), from the occupancy calculator
 int wf_shadow_grid();
 int wf_shade_grid();
 void upload_texture_taps(const float *xy64);  // 32 (x,y) tap offsets of Texture::Sample's elliptical filter
 
-#define QB_BLOCK 128
 
 }  // namespace qb
