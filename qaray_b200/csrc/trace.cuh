@@ -101,8 +101,9 @@ __device__ __forceinline__ float plane_t(const Ray3 &r, float z)
   return t;
 }
 
-// Box::IntersectRay(ray, t_max) for the whole-mesh box (note the non-strict comparisons, unlike the BVH test)
-__device__ __forceinline__ bool mesh_box_hit(const DMesh *__restrict__ m, const Ray3 &r, float t_max)
+// Box::IntersectRay(ray, t_max) for the whole-mesh box (note the non-strict comparisons, unlike the BVH test).
+// exit_out = where the ray leaves the box (QB_BIGFLOAT when every axis is degenerate).
+__device__ __forceinline__ bool mesh_box_hit(const DMesh *__restrict__ m, const Ray3 &r, float t_max, float &exit_out)
 {
   const V3 drcp = v3(1.f, 1.f, 1.f) / r.d;
   const V3 bmin = v3(__ldg(&m->bmin[0]), __ldg(&m->bmin[1]), __ldg(&m->bmin[2]));
@@ -115,6 +116,7 @@ __device__ __forceinline__ bool mesh_box_hit(const DMesh *__restrict__ m, const 
   if (qabs(r.d.z) < 1e-7f) { t0z = -QB_BIGFLOAT; t1z = QB_BIGFLOAT; } else { t0z = qmin(p0.z, p1.z); t1z = qmax(p0.z, p1.z); }
   const float entry = qmax(t0x, qmax(t0y, t0z));
   const float exit = qmin(t1x, qmin(t1y, t1z));
+  exit_out = exit;
   return !(entry > t_max || entry > exit);
 }
 
@@ -238,7 +240,8 @@ __device__ __forceinline__ bool object_test(const DScene &S, const DNode *__rest
   }
   const DMesh *m = &S.meshes[__ldg(&n->mesh)];
   if (__ldg(&m->num_faces) == 0u) return false;
-  if (!mesh_box_hit(m, r, z)) return false;
+  float mexit;
+  if (!mesh_box_hit(m, r, z, mexit)) return false;
   slot = bvh_trace<ANY>(S, __ldg(&m->root_ref), r, z, uv_slot, uv_t, cnt);
   return slot >= 0;
 }

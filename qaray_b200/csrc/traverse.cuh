@@ -48,6 +48,7 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
   Ray3 c0, r;
   V3 drcp = v3(0.f);
   bool gx = false, gy = false, gz = false;
+  float mesh_exit = 0.f;  // where the ray leaves the current mesh's box (bounds the degenerate-axis cull below)
   int k = 0, sp = 0;
   uint32_t cur = QB_REF_EMPTY;
   HitRec h;
@@ -90,8 +91,38 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
         const float t_max = h.z;
         const float entry0 = qmax(t00x, qmax(t00y, t00z)), entry1 = qmax(t10x, qmax(t10y, t10z));
         const float exit0 = qmin(t01x, qmin(t01y, t01z)), exit1 = qmin(t11x, qmin(t11y, t11z));
-        const bool h0 = (entry0 < t_max && entry0 < exit0);
-        const bool h1 = (entry1 < t_max && entry1 < exit1);
+        bool h0 = (entry0 < t_max && entry0 < exit0);
+        bool h1 = (entry1 < t_max && entry1 < exit1);
+        if (gx || gy || gz) {
+          // Degenerate axis (|d| < 1e-7): the reference's slab test ignores that axis altogether, so such a ray would
+          // walk every box its other two axes cross (the exact image-centre ray of sample 0 visits the whole tree, one
+          // dependent load after another: a 20 ms tail). A box the ray cannot reach along that axis holds no
+          // acceptable triangle: an accepted hit point lies inside its triangle's bounds up to rounding, and the ray's
+          // coordinate moves by at most |d| * t with t < min(z, exit of the mesh box). Dropping such boxes changes no
+          // hit, no distance and no order among the boxes that remain. Margin: twice that travel + 1e-4 relative.
+          const float t_far = qmin(t_max, mesh_exit);
+          if (gx) {
+            const float mg = 2.f * qabs(r.d.x) * t_far;
+            const float m0 = mg + 1e-4f * qmax(qabs(r.p.x), qmax(qabs(na.x), qabs(na.w)));
+            const float m1 = mg + 1e-4f * qmax(qabs(r.p.x), qmax(qabs(nb.z), qabs(nc.y)));
+            h0 = h0 && !(r.p.x < na.x - m0 || r.p.x > na.w + m0);
+            h1 = h1 && !(r.p.x < nb.z - m1 || r.p.x > nc.y + m1);
+          }
+          if (gy) {
+            const float mg = 2.f * qabs(r.d.y) * t_far;
+            const float m0 = mg + 1e-4f * qmax(qabs(r.p.y), qmax(qabs(na.y), qabs(nb.x)));
+            const float m1 = mg + 1e-4f * qmax(qabs(r.p.y), qmax(qabs(nb.w), qabs(nc.z)));
+            h0 = h0 && !(r.p.y < na.y - m0 || r.p.y > nb.x + m0);
+            h1 = h1 && !(r.p.y < nb.w - m1 || r.p.y > nc.z + m1);
+          }
+          if (gz) {
+            const float mg = 2.f * qabs(r.d.z) * t_far;
+            const float m0 = mg + 1e-4f * qmax(qabs(r.p.z), qmax(qabs(na.z), qabs(nb.y)));
+            const float m1 = mg + 1e-4f * qmax(qabs(r.p.z), qmax(qabs(nc.x), qabs(nc.w)));
+            h0 = h0 && !(r.p.z < na.z - m0 || r.p.z > nb.y + m0);
+            h1 = h1 && !(r.p.z < nc.x - m1 || r.p.z > nc.w + m1);
+          }
+        }
         if (h0 && h1) {
           const bool first0 = entry0 < entry1;  // the reference pushes the other child first, then this one
           stk[(sp++) * QB_BLOCK] = first0 ? ndr.y : ndr.x;
@@ -143,7 +174,7 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
           obj_slot = -1; uv_slot = -1;
           if (type == QG_OBJ_MESH) {
             const DMesh *m = &S.meshes[__ldg(&nd->mesh)];
-            if (__ldg(&m->num_faces) != 0u && mesh_box_hit(m, r, h.z)) {
+            if (__ldg(&m->num_faces) != 0u && mesh_box_hit(m, r, h.z, mesh_exit)) {
               cur = __ldg(&m->root_ref);
               drcp = v3(1.f, 1.f, 1.f) / r.d;
               gx = qabs(r.d.x) < 1e-7f; gy = qabs(r.d.y) < 1e-7f; gz = qabs(r.d.z) < 1e-7f;
