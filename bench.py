@@ -330,15 +330,21 @@ def finish_b200(args, L):
             peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
         else:
             peak, peak_src = 6650.0, "B200_PROFILING.md fallback (of fallback)"
-        n_launch = max(1, (BOUNCE + 1) * args.steps * max(1, -(-int(t["samples"] / args.steps * 16 / 16) // (1 << 21))))
+        # launches per wave = 1 (stats) + (bounce + 1) x (trace + finish + shade [+ shadow]); waves per step follow
+        per_wave = 1 + (BOUNCE + 1) * (3 + (1 if t["shadow"] > 0 else 0))
+        n_waves = max(1, int(round(t["launches"] / float(args.steps) / per_wave)))
         achieved = kbytes / (kms * 1e-3) * 1e-9 if kms > 0 else 0.0
         traffic = None
-        tp = os.path.join(ROOT, "profiles", "traffic.json")  # dram bytes per launch from the ncu --set full capture, if recorded
+        tp = os.path.join(ROOT, "profiles", "traffic.json")  # DRAM bytes per ray of the kernel from the ncu --set full capture
+        klaunches = max(1, (BOUNCE + 1) * args.steps * n_waves)
         if os.path.exists(tp):
-            traffic = json.load(open(tp)).get(kname.split(" ")[0])
+            rec = json.load(open(tp)).get(kname.split(" ")[0])
+            if rec:
+                krays = t["closest"] if kname.startswith("k_wf_trace") else t["shadow"]
+                traffic = rec["dram_bytes_per_ray"] * krays / klaunches  # per launch, like achieved's bytes
         roofline = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                     "traffic": traffic, "peak_source": peak_src, "bytes_per_ray": klaunch, "kernel_ms_per_step": kms / args.steps,
-                    "launches_of_kernel": n_launch,
+                    "launches_of_kernel": klaunches, "algorithmic_bytes_per_launch": kbytes / klaunches,
                     "per_ray": {"closest": {"nodes": cst["nodes"] / max(1, cst["closest_rays"]), "tris": cst["tris"] / max(1, cst["closest_rays"]),
                                             "objects": cst["objects"] / max(1, cst["closest_rays"]), "bytes": per_c},
                                 "shadow": {"nodes": cst["s_nodes"] / max(1, cst["shadow_rays"]), "tris": cst["s_tris"] / max(1, cst["shadow_rays"]),
