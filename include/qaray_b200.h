@@ -218,6 +218,12 @@ int qg_render_accumulate(qgScene *scene, const qgRenderParams *params, float *d_
 int qg_resolve(qgScene *scene, const qgRenderParams *params, const float *d_accum, const float *d_depth,
                float *rgb_mean, uint8_t *rgb8, float *depth, uint8_t *sample_count, uint8_t *mask, void *stream);
 
+/* Host-only (needs no GPU): how many samples of each pixel the shard described by params renders — the tile loop of
+ * Renderer::ThreadRender (k = mpiRank; k += mpiSize over 4x4 tiles, renderer.cpp:383-398) restricted to
+ * [sample_begin, sample_end). counts[width*height]. The kernels enumerate paths with the same code, so the shards of
+ * all ranks must tile the frame exactly once per sample (tests/test_sharding.py). */
+int qg_shard_coverage(const qgCamera *camera, const qgRenderParams *params, uint16_t *counts);
+
 /* FrameBuffer::SavePNG family (src/fb/framebuffer.cpp:62-143): colour, normalised depth, sample-count images. */
 int qg_save_png_rgb8(const char *path, const uint8_t *rgb8, int32_t width, int32_t height);
 int qg_save_png_depth(const char *path, const float *depth, int32_t width, int32_t height);

@@ -21,7 +21,14 @@ def pytest_configure(config):
 def golden_names():
     if not os.path.isdir(GOLDEN_DIR):
         return []
-    return sorted(f[:-4] for f in os.listdir(GOLDEN_DIR) if f.endswith(".npz"))
+    return sorted(f[:-4] for f in os.listdir(GOLDEN_DIR) if f.endswith(".npz") and not f.startswith("img_"))
+
+
+def image_golden_names():
+    """converged-image fixtures (tools/make_image_golden.py): img_<scene>.npz"""
+    if not os.path.isdir(GOLDEN_DIR):
+        return []
+    return sorted(f[4:-4] for f in os.listdir(GOLDEN_DIR) if f.endswith(".npz") and f.startswith("img_"))
 
 
 def load_golden(name):
