@@ -204,7 +204,7 @@ def run_b200_arm(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        os.environ["NCCL_DEBUG"] = "WARN"  # keep stdout to the one JSON line (NCCL prints its version banner there otherwise)
+        os.environ.pop("NCCL_DEBUG", None)  # any level >= VERSION prints a banner on stdout; stdout carries the one JSON line
         dist.init_process_group("nccl", device_id=dev)
     lib = capi.load()
     capi.check(lib, lib.qg_init(local))

@@ -195,9 +195,18 @@ int upload_scene(qgScene *sc)
       t.a = make_float4(A.x, A.y, A.z, N.x);
       t.b = make_float4(B.x, B.y, B.z, N.y);
       t.c = make_float4(C.x, C.y, C.z, N.z);
-      tris.push_back(t);
       const bool has_uv = m.face_indices[9 * f + 2] >= 0 && m.face_indices[9 * f + 5] >= 0 && m.face_indices[9 * f + 8] >= 0;
-      tri_face.push_back((dm.face_base + f) | (has_uv ? 0x80000000u : 0u));
+      const uint32_t face_word = (dm.face_base + f) | (has_uv ? 0x80000000u : 0u);
+      // per-triangle constants of IntersectTriangle (objects.cpp:235-247), same expressions, no contraction
+      const int axis = tri_axis(N);
+      const float rcp_area = 1.f / tri_area(axis, A, B, C);
+      uint32_t axis_bits = (uint32_t) axis;
+      float axis_f, face_f;
+      memcpy(&axis_f, &axis_bits, 4);
+      memcpy(&face_f, &face_word, 4);
+      t.d = make_float4(rcp_area, axis_f, face_f, 0.f);
+      tris.push_back(t);
+      tri_face.push_back(face_word);
     }
     for (int f = 0; f < m.num_faces; ++f) {
       DFace df;

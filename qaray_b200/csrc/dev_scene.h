@@ -3,7 +3,8 @@
 //   nodes[]      scene-tree nodes in pre-order (src/scene/scene.cpp:50-74 visits them in this order)
 //   obj_node[]   the nodes that hold an object, pre-order; chain[] = for each, its ancestors root-first (root excluded)
 //   bvh[]        64-byte internal nodes: both children's boxes + two child refs (4 x LDG.128 per visit)
-//   tris[]       48-byte triangles in leaf order: A,B,C in xyz and the unit face normal in the three w lanes
+//   tris[]       64-byte triangles in leaf order: A,B,C in xyz, the unit face normal in the three w lanes, and the
+//                per-triangle constants of IntersectTriangle (1/area, dropped axis) + the face word
 //   tri_face[]   global face id of each triangle slot; face_*[] per-face shading attributes (read once per hit)
 #pragma once
 #include <cuda_runtime.h>
@@ -19,6 +20,7 @@ namespace qb {
 #define QB_BIAS 0.005f
 #define QB_MAX_DEPTH 8      // scene-tree depth supported by the chain replay
 #define QB_BLOCK 128        // threads per block of every persistent kernel
+#define QB_MIN_BLOCKS 6      // resident blocks per SM the traversal kernels are compiled for (80 registers, no spills; 8 measured no faster)
 #define QB_STACK 48         // deferred far children per ray = max BVH depth supported (the reference keeps 40 entries, objects.cpp:331)
 
 struct DNode {
@@ -43,8 +45,9 @@ struct DBvhNode {
   uint4 d;   // child0 ref, child1 ref, 0, 0
 };
 
-struct DTri {
+struct DTri {       // 64 B
   float4 a, b, c;  // A.xyz|N.x  B.xyz|N.y  C.xyz|N.z
+  float4 d;        // 1 / TriangleArea(axis, A, B, C), axis (int bits), tri_face word (uint bits), 0
 };
 
 struct DFace {      // 64 B

@@ -57,6 +57,22 @@ QB_HD float qmin(float x, float y) { return x < y ? x : y; }
 QB_HD float qmax(float x, float y) { return x > y ? x : y; }
 QB_HD float qabs(float x) { return x > 0 ? x : -x; }
 
+// TriangleArea (src/objects/objects.cpp:30-41): signed projected area (x2) with `axis` dropped, and the axis
+// IntersectTriangle drops: the one where abs(N) is largest (objects.cpp:235-247)
+QB_HD float tri_area(int axis, V3 A, V3 B, V3 C)
+{
+  if (axis == 0) return (B.y - A.y) * (C.z - A.z) - (C.y - A.y) * (B.z - A.z);
+  if (axis == 1) return (B.x - A.x) * (C.z - A.z) - (C.x - A.x) * (B.z - A.z);
+  return (B.x - A.x) * (C.y - A.y) - (C.x - A.x) * (B.y - A.y);
+}
+QB_HD int tri_axis(V3 N)
+{
+  const float ax = qabs(N.x), ay = qabs(N.y), az = qabs(N.z);
+  if (ax > ay && ax > az) return 0;
+  if (ay > az) return 1;
+  return 2;
+}
+
 // column-major 3x3: c[col][row], like glm::mat3
 struct M3 {
   float c[3][3];

@@ -120,20 +120,6 @@ __device__ __forceinline__ bool mesh_box_hit(const DMesh *__restrict__ m, const 
   return !(entry > t_max || entry > exit);
 }
 
-__device__ __forceinline__ float tri_area(int axis, V3 A, V3 B, V3 C)  // TriangleArea, objects.cpp:30-41
-{
-  if (axis == 0) return (B.y - A.y) * (C.z - A.z) - (C.y - A.y) * (B.z - A.z);
-  if (axis == 1) return (B.x - A.x) * (C.z - A.z) - (C.x - A.x) * (B.z - A.z);
-  return (B.x - A.x) * (C.y - A.y) - (C.x - A.x) * (B.y - A.y);
-}
-__device__ __forceinline__ int tri_axis(V3 N)
-{
-  const float ax = qabs(N.x), ay = qabs(N.y), az = qabs(N.z);
-  if (ax > ay && ax > az) return 0;
-  if (ay > az) return 1;
-  return 2;
-}
-
 // IntersectTriangle up to the acceptance decision. N is the unit face normal the reference recomputes per test,
 // here computed once on the host with the same expression. Returns accepted t or a negative number.
 __device__ __forceinline__ float tri_t(const Ray3 &r, float z, V3 A, V3 B, V3 C, V3 N)
@@ -152,6 +138,30 @@ __device__ __forceinline__ float tri_t(const Ray3 &r, float z, V3 A, V3 B, V3 C,
   const float c = 1.f - a - b;
   if (a < 0 || b < 0 || c < 0) return -1.f;
   return t;
+}
+
+// The same decision without early exits: every lane of a converged LEAF phase runs one instruction stream. s and axis
+// are the per-triangle constants 1 / TriangleArea(axis, A, B, C) and the dropped axis, computed on the host with the
+// same expressions. Values computed past a failed check are never used (ok is false), so NaN/inf there are harmless.
+__device__ __forceinline__ bool tri_accept(const Ray3 &r, float z, V3 A, V3 B, V3 C, V3 N, float s, int axis, float &t_out)
+{
+  const float dz = dot(r.d, N);
+  const float pz = dot(r.p - A, N);
+  const float t = -pz / dz;
+  bool ok = !(qabs(dz) < 1e-7f) && !(t <= QB_BIAS) && (z > t);
+  const V3 p = r.p + t * r.d;
+  // coordinates kept by the projection: axis 0 -> (y, z), 1 -> (x, z), 2 -> (x, y)
+  const bool a0 = axis == 0, a2 = axis == 2;
+  const float pu = a0 ? p.y : p.x, pv = a2 ? p.y : p.z;
+  const float Au = a0 ? A.y : A.x, Av = a2 ? A.y : A.z;
+  const float Bu = a0 ? B.y : B.x, Bv = a2 ? B.y : B.z;
+  const float Cu = a0 ? C.y : C.x, Cv = a2 ? C.y : C.z;
+  const float a = ((Bu - pu) * (Cv - pv) - (Cu - pu) * (Bv - pv)) * s;   // TriangleArea(axis, p, B, C) * s
+  const float b = ((Cu - pu) * (Av - pv) - (Au - pu) * (Cv - pv)) * s;   // TriangleArea(axis, p, C, A) * s
+  const float c = 1.f - a - b;
+  ok = ok && !(a < 0 || b < 0 || c < 0);
+  t_out = t;
+  return ok;
 }
 
 // TraceBVHNode. ANY = stop at the first accepted triangle (the reference finishes the traversal, but its

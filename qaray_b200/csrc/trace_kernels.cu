@@ -113,7 +113,7 @@ struct WfShadowIO {
 
 // PRIMARY = depth 0 (rays generated in registers) / depth >= 1 (rays read from the path state): two instantiations.
 template <bool PRIMARY>
-__global__ void __launch_bounds__(QB_BLOCK) k_wf_trace(const DScene S, const WfBuffers B, const WfParams P)
+__global__ void __launch_bounds__(QB_BLOCK, QB_MIN_BLOCKS) k_wf_trace(const DScene S, const WfBuffers B, const WfParams P)
 {
   __shared__ uint32_t s_stack[QB_STACK * QB_BLOCK];
   TraceCounters cnt = {0, 0, 0};
@@ -155,7 +155,7 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_finish(const DScene S, const Wf
   }
 }
 
-__global__ void __launch_bounds__(QB_BLOCK) k_wf_shadow(const DScene S, const WfBuffers B, const WfParams P)
+__global__ void __launch_bounds__(QB_BLOCK, QB_MIN_BLOCKS) k_wf_shadow(const DScene S, const WfBuffers B, const WfParams P)
 {
   __shared__ uint32_t s_stack[QB_STACK * QB_BLOCK];
   TraceCounters cnt = {0, 0, 0};

@@ -18,6 +18,7 @@
 namespace qb {
 
 #define QB_REF_EMPTY 0x7FFFFFFFu   // "no current node" (an internal index never reaches 2^31-1)
+#define QB_INNER_REPS 3            // node visits per vote while the inner group holds together
 
 // what the closest-hit traversal leaves per ray; attributes are computed later by finish_hit (full warps)
 struct HitRec {
@@ -72,85 +73,100 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
     const int n_fetch = __popc(m_fetch), n_inner = __popc(m_inner), n_leaf = __popc(m_leaf), n_next = __popc(m_next);
 
     if (n_inner >= n_leaf && n_inner >= n_next && n_inner >= n_fetch) {
-      // ---- INNER: one node visit (both children's boxes), near child becomes current, far child is deferred --------
-      if (s_inner) {
-        const DBvhNode *np = &S.bvh[cur];
-        const float4 na = __ldg(&np->a), nb = __ldg(&np->b), nc = __ldg(&np->c);
-        const uint4 ndr = __ldg(&np->d);
-        QB_CNT(nodes);
-        const float p00x = -(r.p.x - na.x) * drcp.x, p00y = -(r.p.y - na.y) * drcp.y, p00z = -(r.p.z - na.z) * drcp.z;
-        const float p01x = -(r.p.x - na.w) * drcp.x, p01y = -(r.p.y - nb.x) * drcp.y, p01z = -(r.p.z - nb.y) * drcp.z;
-        const float p10x = -(r.p.x - nb.z) * drcp.x, p10y = -(r.p.y - nb.w) * drcp.y, p10z = -(r.p.z - nc.x) * drcp.z;
-        const float p11x = -(r.p.x - nc.y) * drcp.x, p11y = -(r.p.y - nc.z) * drcp.y, p11z = -(r.p.z - nc.w) * drcp.z;
-        const float t00x = gx ? -QB_BIGFLOAT : qmin(p00x, p01x), t01x = gx ? QB_BIGFLOAT : qmax(p00x, p01x);
-        const float t10x = gx ? -QB_BIGFLOAT : qmin(p10x, p11x), t11x = gx ? QB_BIGFLOAT : qmax(p10x, p11x);
-        const float t00y = gy ? -QB_BIGFLOAT : qmin(p00y, p01y), t01y = gy ? QB_BIGFLOAT : qmax(p00y, p01y);
-        const float t10y = gy ? -QB_BIGFLOAT : qmin(p10y, p11y), t11y = gy ? QB_BIGFLOAT : qmax(p10y, p11y);
-        const float t00z = gz ? -QB_BIGFLOAT : qmin(p00z, p01z), t01z = gz ? QB_BIGFLOAT : qmax(p00z, p01z);
-        const float t10z = gz ? -QB_BIGFLOAT : qmin(p10z, p11z), t11z = gz ? QB_BIGFLOAT : qmax(p10z, p11z);
-        const float t_max = h.z;
-        const float entry0 = qmax(t00x, qmax(t00y, t00z)), entry1 = qmax(t10x, qmax(t10y, t10z));
-        const float exit0 = qmin(t01x, qmin(t01y, t01z)), exit1 = qmin(t11x, qmin(t11y, t11z));
-        bool h0 = (entry0 < t_max && entry0 < exit0);
-        bool h1 = (entry1 < t_max && entry1 < exit1);
-        if (gx || gy || gz) {
-          // Degenerate axis (|d| < 1e-7): the reference's slab test ignores that axis altogether, so such a ray would
-          // walk every box its other two axes cross (the exact image-centre ray of sample 0 visits the whole tree, one
-          // dependent load after another: a 20 ms tail). A box the ray cannot reach along that axis holds no
-          // acceptable triangle: an accepted hit point lies inside its triangle's bounds up to rounding, and the ray's
-          // coordinate moves by at most |d| * t with t < min(z, exit of the mesh box). Dropping such boxes changes no
-          // hit, no distance and no order among the boxes that remain. Margin: twice that travel + 1e-4 relative.
-          const float t_far = qmin(t_max, mesh_exit);
-          if (gx) {
-            const float mg = 2.f * qabs(r.d.x) * t_far;
-            const float m0 = mg + 1e-4f * qmax(qabs(r.p.x), qmax(qabs(na.x), qabs(na.w)));
-            const float m1 = mg + 1e-4f * qmax(qabs(r.p.x), qmax(qabs(nb.z), qabs(nc.y)));
-            h0 = h0 && !(r.p.x < na.x - m0 || r.p.x > na.w + m0);
-            h1 = h1 && !(r.p.x < nb.z - m1 || r.p.x > nc.y + m1);
+      // ---- INNER: node visits (both children's boxes); the near child becomes current, the far child is deferred.
+      // Up to QB_INNER_REPS visits per vote while at least half of the lanes that started are still on inner nodes.
+#pragma unroll 1
+      for (int rep = 0; rep < QB_INNER_REPS; ++rep) {
+        const bool go = active && cur != QB_REF_EMPTY && !(cur & QB_LEAF_BIT);
+        if (rep > 0 && 2 * __popc(__ballot_sync(0xFFFFFFFFu, go)) < n_inner) break;
+        if (go) {
+          const DBvhNode *np = &S.bvh[cur];
+          const float4 na = __ldg(&np->a), nb = __ldg(&np->b), nc = __ldg(&np->c);
+          const uint4 ndr = __ldg(&np->d);
+          QB_CNT(nodes);
+          const float p00x = -(r.p.x - na.x) * drcp.x, p00y = -(r.p.y - na.y) * drcp.y, p00z = -(r.p.z - na.z) * drcp.z;
+          const float p01x = -(r.p.x - na.w) * drcp.x, p01y = -(r.p.y - nb.x) * drcp.y, p01z = -(r.p.z - nb.y) * drcp.z;
+          const float p10x = -(r.p.x - nb.z) * drcp.x, p10y = -(r.p.y - nb.w) * drcp.y, p10z = -(r.p.z - nc.x) * drcp.z;
+          const float p11x = -(r.p.x - nc.y) * drcp.x, p11y = -(r.p.y - nc.z) * drcp.y, p11z = -(r.p.z - nc.w) * drcp.z;
+          const float t_max = h.z;
+          float entry0, entry1, exit0, exit1;
+          bool h0, h1;
+          if (!(gx || gy || gz)) {
+            // no degenerate axis: every p is finite or +-inf, never NaN, so the reference's MIN/MAX macros
+            // (x < y ? x : y) and fminf/fmaxf pick the same value up to the sign of a zero, which no comparison sees
+            entry0 = fmaxf(fminf(p00x, p01x), fmaxf(fminf(p00y, p01y), fminf(p00z, p01z)));
+            entry1 = fmaxf(fminf(p10x, p11x), fmaxf(fminf(p10y, p11y), fminf(p10z, p11z)));
+            exit0 = fminf(fmaxf(p00x, p01x), fminf(fmaxf(p00y, p01y), fmaxf(p00z, p01z)));
+            exit1 = fminf(fmaxf(p10x, p11x), fminf(fmaxf(p10y, p11y), fmaxf(p10z, p11z)));
+            h0 = (entry0 < t_max && entry0 < exit0);
+            h1 = (entry1 < t_max && entry1 < exit1);
+          } else {
+            const float t00x = gx ? -QB_BIGFLOAT : qmin(p00x, p01x), t01x = gx ? QB_BIGFLOAT : qmax(p00x, p01x);
+            const float t10x = gx ? -QB_BIGFLOAT : qmin(p10x, p11x), t11x = gx ? QB_BIGFLOAT : qmax(p10x, p11x);
+            const float t00y = gy ? -QB_BIGFLOAT : qmin(p00y, p01y), t01y = gy ? QB_BIGFLOAT : qmax(p00y, p01y);
+            const float t10y = gy ? -QB_BIGFLOAT : qmin(p10y, p11y), t11y = gy ? QB_BIGFLOAT : qmax(p10y, p11y);
+            const float t00z = gz ? -QB_BIGFLOAT : qmin(p00z, p01z), t01z = gz ? QB_BIGFLOAT : qmax(p00z, p01z);
+            const float t10z = gz ? -QB_BIGFLOAT : qmin(p10z, p11z), t11z = gz ? QB_BIGFLOAT : qmax(p10z, p11z);
+            entry0 = qmax(t00x, qmax(t00y, t00z)); entry1 = qmax(t10x, qmax(t10y, t10z));
+            exit0 = qmin(t01x, qmin(t01y, t01z)); exit1 = qmin(t11x, qmin(t11y, t11z));
+            h0 = (entry0 < t_max && entry0 < exit0);
+            h1 = (entry1 < t_max && entry1 < exit1);
+            // Degenerate axis (|d| < 1e-7): the reference's slab test ignores that axis altogether, so such a ray would
+            // walk every box its other two axes cross (the exact image-centre ray of sample 0 visits the whole tree, one
+            // dependent load after another: a 20 ms tail). A box the ray cannot reach along that axis holds no
+            // acceptable triangle: an accepted hit point lies inside its triangle's bounds up to rounding, and the ray's
+            // coordinate moves by at most |d| * t with t < min(z, exit of the mesh box). Dropping such boxes changes no
+            // hit, no distance and no order among the boxes that remain. Margin: twice that travel + 1e-4 relative.
+            const float t_far = qmin(t_max, mesh_exit);
+            if (gx) {
+              const float mg = 2.f * qabs(r.d.x) * t_far;
+              const float m0 = mg + 1e-4f * qmax(qabs(r.p.x), qmax(qabs(na.x), qabs(na.w)));
+              const float m1 = mg + 1e-4f * qmax(qabs(r.p.x), qmax(qabs(nb.z), qabs(nc.y)));
+              h0 = h0 && !(r.p.x < na.x - m0 || r.p.x > na.w + m0);
+              h1 = h1 && !(r.p.x < nb.z - m1 || r.p.x > nc.y + m1);
+            }
+            if (gy) {
+              const float mg = 2.f * qabs(r.d.y) * t_far;
+              const float m0 = mg + 1e-4f * qmax(qabs(r.p.y), qmax(qabs(na.y), qabs(nb.x)));
+              const float m1 = mg + 1e-4f * qmax(qabs(r.p.y), qmax(qabs(nb.w), qabs(nc.z)));
+              h0 = h0 && !(r.p.y < na.y - m0 || r.p.y > nb.x + m0);
+              h1 = h1 && !(r.p.y < nb.w - m1 || r.p.y > nc.z + m1);
+            }
+            if (gz) {
+              const float mg = 2.f * qabs(r.d.z) * t_far;
+              const float m0 = mg + 1e-4f * qmax(qabs(r.p.z), qmax(qabs(na.z), qabs(nb.y)));
+              const float m1 = mg + 1e-4f * qmax(qabs(r.p.z), qmax(qabs(nc.x), qabs(nc.w)));
+              h0 = h0 && !(r.p.z < na.z - m0 || r.p.z > nb.y + m0);
+              h1 = h1 && !(r.p.z < nc.x - m1 || r.p.z > nc.w + m1);
+            }
           }
-          if (gy) {
-            const float mg = 2.f * qabs(r.d.y) * t_far;
-            const float m0 = mg + 1e-4f * qmax(qabs(r.p.y), qmax(qabs(na.y), qabs(nb.x)));
-            const float m1 = mg + 1e-4f * qmax(qabs(r.p.y), qmax(qabs(nb.w), qabs(nc.z)));
-            h0 = h0 && !(r.p.y < na.y - m0 || r.p.y > nb.x + m0);
-            h1 = h1 && !(r.p.y < nb.w - m1 || r.p.y > nc.z + m1);
+          if (h0 && h1) {
+            const bool first0 = entry0 < entry1;  // the reference pushes the other child first, then this one
+            stk[(sp++) * QB_BLOCK] = first0 ? ndr.y : ndr.x;
+            cur = first0 ? ndr.x : ndr.y;
+          } else if (h0 || h1) {
+            cur = h0 ? ndr.x : ndr.y;
+          } else {
+            cur = sp > 0 ? stk[(--sp) * QB_BLOCK] : QB_REF_EMPTY;
           }
-          if (gz) {
-            const float mg = 2.f * qabs(r.d.z) * t_far;
-            const float m0 = mg + 1e-4f * qmax(qabs(r.p.z), qmax(qabs(na.z), qabs(nb.y)));
-            const float m1 = mg + 1e-4f * qmax(qabs(r.p.z), qmax(qabs(nc.x), qabs(nc.w)));
-            h0 = h0 && !(r.p.z < na.z - m0 || r.p.z > nb.y + m0);
-            h1 = h1 && !(r.p.z < nc.x - m1 || r.p.z > nc.w + m1);
-          }
-        }
-        if (h0 && h1) {
-          const bool first0 = entry0 < entry1;  // the reference pushes the other child first, then this one
-          stk[(sp++) * QB_BLOCK] = first0 ? ndr.y : ndr.x;
-          cur = first0 ? ndr.x : ndr.y;
-        } else if (h0) {
-          cur = ndr.x;
-        } else if (h1) {
-          cur = ndr.y;
-        } else {
-          cur = sp > 0 ? stk[(--sp) * QB_BLOCK] : QB_REF_EMPTY;
         }
       }
     } else if (n_leaf >= n_next && n_leaf >= n_fetch) {
-      // ---- LEAF: the leaf's triangles in elements[] order -------------------------------------------------------------
+      // ---- LEAF: the leaf's triangles in elements[] order, branch-free per triangle ------------------------------------
       if (s_leaf) {
         const uint32_t base = cur & 0x0FFFFFFFu;
         const uint32_t count = ((cur >> 28) & 7u) + 1u;
         cur = sp > 0 ? stk[(--sp) * QB_BLOCK] : QB_REF_EMPTY;
         for (uint32_t i = 0; i < count; ++i) {
           const DTri *tp = &S.tris[base + i];
-          const float4 ta = __ldg(&tp->a), tb = __ldg(&tp->b), tc = __ldg(&tp->c);
+          const float4 ta = __ldg(&tp->a), tb = __ldg(&tp->b), tc = __ldg(&tp->c), td = __ldg(&tp->d);
           QB_CNT(tris);
-          const float t = tri_t(r, h.z, xyz(ta), xyz(tb), xyz(tc), v3(ta.w, tb.w, tc.w));
-          if (t > 0.f) {
+          float t;
+          if (tri_accept(r, h.z, xyz(ta), xyz(tb), xyz(tc), v3(ta.w, tb.w, tc.w), td.x, __float_as_int(td.y), t)) {
             if (ANY) { io.store_any(idx, true); active = false; break; }
             h.z = t;
             obj_slot = (int) (base + i);
-            if (__ldg(&S.tri_face[base + i]) & 0x80000000u) { uv_slot = obj_slot; uv_t = t; }
+            if (__float_as_uint(td.z) & 0x80000000u) { uv_slot = obj_slot; uv_t = t; }
           }
         }
       }
