@@ -36,6 +36,10 @@ enum { QG_TEX_NULL = 0, QG_TEX_CHECKER = 1, QG_TEX_IMAGE = 2 };
 /* material kinds: MtlBlinn (alias of MtlBlinn_PhotonMap, src/materials/materials.h:57) and MultiMtl (:65-87) */
 enum { QG_MTL_BLINN = 0, QG_MTL_MULTI = 1 };
 
+/* the classes `MtlBlinn` can alias (src/materials/materials.h:57-61): MtlBlinn_PhotonMap (.cpp:256-500, photon maps off),
+ * MtlBlinn_PathTracing (.cpp:69-300), MtlBlinn_MonteCarloGI (.cpp:34-266), MtlBlinn_Basic (.cpp:30-185), MtlPhong_Basic */
+enum { QG_CLASS_PHOTONMAP = 0, QG_CLASS_PATHTRACING = 1, QG_CLASS_MONTECARLOGI = 2, QG_CLASS_BLINN_BASIC = 3, QG_CLASS_PHONG_BASIC = 4 };
+
 /* Transformation (src/core/transform.h:36-79). Matrices column-major like glm::mat3. */
 typedef struct qgXform {
   float tm[9];
@@ -146,7 +150,9 @@ typedef struct qgRenderParams {
   int32_t tile_rank, tile_ranks; /* Renderer::mpiRank / mpiSize: this shard renders 4x4 tiles k = rank (mod ranks) (renderer.cpp:383-387) */
   int32_t sample_begin, sample_end; /* sample-index shard [begin,end); 0,0 = [0,spp) */
   int32_t batch_paths; /* paths in flight per wave; 0 = default */
-  int32_t sort_by_material; /* 1 = counting-sort the shade queue by material id */
+  int32_t sort_by_material; /* reserved, must be 0 */
+  int32_t material_class; /* QG_CLASS_*: which MtlBlinn class shades `blinn` materials (the reference picks it with a
+                             compile-time alias, src/materials/materials.h:57-61); 0 = MtlBlinn_PhotonMap, its default */
 } qgRenderParams;
 
 typedef struct qgRenderStats {

@@ -22,17 +22,28 @@ HIT_DTYPE = np.dtype([
 assert HIT_DTYPE.itemsize == 88
 
 
-def available():
-    return os.path.exists(REF_SO)
+# qgRenderParams.material_class -> oracle build variant
+VARIANTS = {0: "", 1: "pathtracing", 2: "montecarlogi", 3: "blinn_basic", 4: "phong_basic"}
+
+
+def variant_so(variant=""):
+    return REF_SO if not variant else os.path.join(REF_DIR, "libqaref_parity_%s.so" % variant)
+
+
+def available(variant=""):
+    return os.path.exists(variant_so(variant))
 
 
 class Ref:
     """One loaded reference scene (process-global)."""
 
-    def __init__(self):
-        if not available():
-            raise RuntimeError("oracle/_ref/libqaref_parity.so missing: run `make -C oracle ref` where /root/reference exists")
-        self.lib = C.CDLL(REF_SO)
+    def __init__(self, variant=""):
+        """variant: "" = the reference as shipped (MtlBlinn = MtlBlinn_PhotonMap), or one of VARIANTS = the same build with
+        the alias at src/materials/materials.h:57 switched to that class"""
+        so = variant_so(variant)
+        if not os.path.exists(so):
+            raise RuntimeError("%s missing: run `make -C oracle ref` where /root/reference exists" % so)
+        self.lib = C.CDLL(so)
         L = self.lib
         L.qaref_load.argtypes = [C.c_char_p, C.c_char_p, C.c_int]
         L.qaref_load.restype = C.c_int

@@ -375,9 +375,9 @@ int upload_scene(qgScene *sc)
 // ---------------------------------------------------------------------------------------------- render driver
 namespace {
 
-int ensure_wf(qgScene *sc, uint32_t capacity)
+int ensure_wf(qgScene *sc, uint32_t capacity, bool carry_diff = false)
 {
-  if (sc->wf_capacity == capacity) return QG_OK;
+  if (sc->wf_capacity == capacity && (!carry_diff || sc->wf.h4 != nullptr)) return QG_OK;
   for (void *p : sc->wf_allocs) cudaFree(p);
   sc->wf_allocs.clear();
   sc->wf_capacity = 0;
@@ -399,6 +399,14 @@ int ensure_wf(qgScene *sc, uint32_t capacity)
   CU(alloc4(&B.h1, capacity));
   CU(alloc4(&B.h2, capacity));
   CU(alloc4(&B.h3, capacity));
+  if (carry_diff) {  // differential rays of secondary paths (Whitted-style material classes)
+    for (int k = 0; k < 2; ++k) {
+      CU(alloc4(&B.ps4[k], capacity));
+      CU(alloc4(&B.ps5[k], capacity));
+      CU(alloc4(&B.ps6[k], capacity));
+    }
+    CU(alloc4(&B.h4, capacity));
+  }
   CU(alloc4(&B.s0, shadow_cap));
   CU(alloc4(&B.s1, shadow_cap));
   CU(alloc4(&B.s2, shadow_cap));
@@ -427,6 +435,8 @@ void camera_frame(const qgCamera &cam, int W, int H, V3 *U, V3 *Vv, V3 *A)
   *Vv = -Y * (screenH / H);
   *A = pos - Z * focal + Y * screenH / 2.f - X * screenW / 2.f;
 }
+
+bool class_carries_diff(int cls) { return cls == QG_CLASS_MONTECARLOGI || cls == QG_CLASS_BLINN_BASIC || cls == QG_CLASS_PHONG_BASIC; }
 
 struct Shard {
   int W, H, tiles_x, tiles_y, tiles_local, s0, s1;
@@ -475,7 +485,27 @@ int make_params(const qgScene *sc, const qgRenderParams *rp, WfParams *P, Shard 
   P->seed = rp->seed;
   P->max_bounce = rp->max_bounce;
   P->stale_tex = 1;
+  if (rp->material_class < QG_CLASS_PHOTONMAP || rp->material_class > QG_CLASS_PHONG_BASIC) return fail(QG_EINVAL, "unknown material_class");
+  P->mtl_class = rp->material_class;
+  P->carry_diff = class_carries_diff(rp->material_class) ? 1 : 0;
+  // the constructors of MtlBlinn_Basic / MtlPhong_Basic switch the lights' inverse-square falloff off for the whole
+  // process (MtlBlinn_Basic.cpp:18, lights.cpp:18-30); it happens as soon as the scene file declares one material
+  P->no_falloff = (rp->material_class == QG_CLASS_BLINN_BASIC || rp->material_class == QG_CLASS_PHONG_BASIC) && !sc->flat.materials.empty();
   return QG_OK;
+}
+
+// Worst-case number of paths at any depth per primary path: the Whitted-style classes spawn a refraction and a
+// reflection ray per hit, MtlBlinn_MonteCarloGI adds 10 hemisphere samples at depth 0 and 1 below (:176-178). The wave
+// size is the buffer capacity divided by this, so no queue can overflow whatever the scene does.
+unsigned long long class_growth(int cls, int max_bounce)
+{
+  unsigned long long g = 1, worst = 1;
+  for (int d = 0; d < max_bounce; ++d) {
+    if (cls == QG_CLASS_BLINN_BASIC || cls == QG_CLASS_PHONG_BASIC) g *= 2ull;
+    else if (cls == QG_CLASS_MONTECARLOGI) g *= (d == 0 ? 12ull : 3ull);
+    worst = std::max(worst, g);
+  }
+  return worst;
 }
 
 // Per-kernel-class device time: one timestamp event after every launch (class = 0 trace, 1 shade, 2 shadow,
@@ -544,12 +574,17 @@ int render_accumulate(qgScene *sc, const qgRenderParams *rp, float *d_accum, flo
   // shadow-queue state (12 + 3 * lights float4 per path), at most 2^26 paths.
   uint32_t cap = (uint32_t) rp->batch_paths;
   if (rp->batch_paths <= 0) {
-    const unsigned long long per_path = 16ull * (12ull + 3ull * (unsigned long long) std::max(1, sc->dev.num_nonambient));
+    const unsigned long long per_path = 16ull * ((P.carry_diff ? 19ull : 12ull) + 3ull * (unsigned long long) std::max(1, sc->dev.num_nonambient));
     cap = (uint32_t) std::min<unsigned long long>(1ull << 26, (16ull << 30) / per_path);
   }
   cap = (cap + 31u) & ~31u;
-  if ((unsigned long long) cap > sh.total_paths) cap = (uint32_t) std::max<unsigned long long>(32ull, (sh.total_paths + 31ull) & ~31ull);
-  rc = ensure_wf(sc, cap);
+  // paths per wave: the capacity over the class's worst-case growth (1 for the two path-tracing classes)
+  const unsigned long long growth = class_growth(P.mtl_class, P.max_bounce);
+  uint32_t wave = (uint32_t) std::max<unsigned long long>(32ull, ((unsigned long long) cap / growth) & ~31ull);
+  if ((unsigned long long) wave > sh.total_paths) wave = (uint32_t) std::max<unsigned long long>(32ull, (sh.total_paths + 31ull) & ~31ull);
+  if ((unsigned long long) wave * growth > (1ull << 31)) return fail(QG_EINVAL, "max_bounce too deep for this material class");
+  cap = (uint32_t) ((unsigned long long) wave * growth);
+  rc = ensure_wf(sc, cap, P.carry_diff != 0);
   if (rc) return rc;
   P.accum = d_accum;
   P.depth_plane = d_depth;
@@ -560,9 +595,9 @@ int render_accumulate(qgScene *sc, const qgRenderParams *rp, float *d_accum, flo
   CU(cudaEventRecord(e0, st));
   uint64_t launches = 0;
   KernelClock clk{sc, st, stats != nullptr};
-  for (unsigned long long base = 0; base < sh.total_paths; base += cap) {
+  for (unsigned long long base = 0; base < sh.total_paths; base += wave) {
     P.wave_base = base;
-    P.n_paths = (uint32_t) std::min<unsigned long long>(cap, sh.total_paths - base);
+    P.n_paths = (uint32_t) std::min<unsigned long long>(wave, sh.total_paths - base);
     run_wave(sc, P, st, &launches, &clk);
   }
   CU(cudaEventRecord(e1, st));

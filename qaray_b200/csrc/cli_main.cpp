@@ -1,7 +1,7 @@
 // cli_main.cpp — main.cpp-style driver for the B200 path: same flags as the reference's CLI
 // (src/main.cpp:17-44: -spp N, -sppMin N, -sppMax N, -bounce N, -srgb 0|1, <scene.xml>; -batch is implied, there is
 // no GUI), plus -assets DIR (where the XML's relative .obj/.png names resolve), -size W H, -seed S, -device D,
-// -shard RANK SIZE (Renderer::mpiRank / mpiSize) and -out PREFIX. Writes colorBuffer.png / depthBuffer.png /
+// -shard RANK SIZE (Renderer::mpiRank / mpiSize), -mtl CLASS (which class MtlBlinn names) and -out PREFIX. Writes colorBuffer.png / depthBuffer.png /
 // sampleBuffer.png like Renderer_MPI::Render and prints one line of ray statistics.
 #include <cstring>
 #include <string>
@@ -42,6 +42,15 @@ int main(int argc, char **argv)
     else if (s == "-device") device = atoi(next());
     else if (s == "-size") { param.width = atoi(next()); param.height = atoi(next()); }
     else if (s == "-shard") { rank = atoi(next()); size = atoi(next()); }
+    else if (s == "-mtl") {  // the reference's compile-time `using MtlBlinn = ...` (materials.h:57-61)
+      const std::string c(next());
+      if (c == "photonmap") param.materialClass = QG_CLASS_PHOTONMAP;
+      else if (c == "pathtracing") param.materialClass = QG_CLASS_PATHTRACING;
+      else if (c == "montecarlogi") param.materialClass = QG_CLASS_MONTECARLOGI;
+      else if (c == "blinn_basic") param.materialClass = QG_CLASS_BLINN_BASIC;
+      else if (c == "phong_basic") param.materialClass = QG_CLASS_PHONG_BASIC;
+      else { fprintf(stderr, "Error: unknown material class %s\n", c.c_str()); return -1; }
+    }
     else file = argv[i];
   }
   if (!file) {

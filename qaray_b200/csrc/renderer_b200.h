@@ -26,6 +26,9 @@ struct RendererParam {
   int maxBounce = 5;  // Material::maxBounce (src/core/material.cpp:31)
   unsigned seed = 0x5EEDu;
   int width = 0, height = 0;  // 0 = the XML camera's
+  // which class `MtlBlinn` names: a compile-time alias in the reference (src/materials/materials.h:57-61), a run-time
+  // switch here (QG_CLASS_*); default = MtlBlinn_PhotonMap like the reference's build
+  int materialClass = QG_CLASS_PHOTONMAP;
   void SetPhotonMappingFlag(bool f) { usePhotonMap = f; }
   void SetPhotonMapSize(size_t s) { photonMapSize = s; }
   void SetCausticsMapSize(size_t s) { causticsMapSize = s; }
@@ -100,6 +103,7 @@ class Renderer_B200 {
     rp.height = (int32_t) pixelH;
     rp.tile_rank = (int32_t) mpiRank;
     rp.tile_ranks = (int32_t) mpiSize;
+    rp.material_class = param.materialClass;
     if (qg_render(scene, &rp, linearBuffer.data(), colorBuffer.data(), depthBuffer.data(), sampleCountBuffer.data(), maskBuffer.data(),
                   &stats) != QG_OK) {
       fprintf(stderr, "Renderer_B200::Render: %s\n", qg_last_error());

@@ -13,7 +13,9 @@
 // Random numbers: a counter-based stream per (pixel, sample) drawn in the order the reference's recursion draws
 // them (lobe selection, then the lobe's direction sample, then the next hit...), so the same stream fed to the
 // reference gives the same path.
+#include <cstdio>
 #include "wavefront.h"
+#include "trace.cuh"  // Ray3
 
 namespace qb {
 
@@ -29,9 +31,14 @@ struct Rng {
 __device__ __forceinline__ V3 ld3(const float *p) { return v3(p[0], p[1], p[2]); }
 
 // ---- textures ---------------------------------------------------------------------------------------------------
+// (int) x as the reference's x86-64 build evaluates it (cvttss2si): out-of-range and NaN give INT_MIN, where CUDA's
+// conversion would saturate. Differential rays that leave a refracting object almost parallel to a textured plane
+// produce texture-space footprints beyond 2^31, so the difference is visible (example_project7_object through glass).
+__device__ __forceinline__ int cvt_int(float x) { return fabsf(x) < 2147483648.f ? (int) x : (int) 0x80000000; }
+
 __device__ __forceinline__ V3 tile_clamp(V3 uvw)  // Texture::TileClamp, core/texture.cpp:53-63
 {
-  V3 u = v3(uvw.x - (float) (int) uvw.x, uvw.y - (float) (int) uvw.y, uvw.z - (float) (int) uvw.z);
+  V3 u = v3(uvw.x - (float) cvt_int(uvw.x), uvw.y - (float) cvt_int(uvw.y), uvw.z - (float) cvt_int(uvw.z));
   if (u.x < 0) u.x += 1;
   if (u.y < 0) u.y += 1;
   if (u.z < 0) u.z += 1;
@@ -58,7 +65,7 @@ __device__ V3 texture_fetch(const DScene &S, const DTexture &t, V3 uvw)
   const int width = t.width, height = t.height;
   const float x = width * u.x;
   const float y = height * u.y;
-  int ix = (int) x, iy = (int) y;
+  int ix = cvt_int(x), iy = cvt_int(y);
   const float fx = x - ix, fy = y - iy;
   if (ix < 0) ix -= (ix / width - 1) * width;
   if (ix >= width) ix -= (ix / width) * width;
@@ -160,8 +167,6 @@ __device__ __forceinline__ float spot_attenuation(const DLight &l, V3 dir)
 
 enum { SEL_TRANSMIT = 0, SEL_REFLECT = 1, SEL_DIFFUSE = 2, SEL_ABSORB = 3 };
 
-#define QB_FLAG_DIFFUSE_HIT 1u
-
 __device__ __forceinline__ void accum_add(float *accum, int slot, V3 c)
 {
   float *a = accum + 4ll * slot;
@@ -173,7 +178,7 @@ __device__ __forceinline__ void accum_add(float *accum, int slot, V3 c)
 __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade(const DScene S, const WfBuffers B, const WfParams P)
 {
   const int d = P.depth;
-  const uint32_t n = d == 0 ? P.n_paths : B.counters[QB_CNT_PATHS + d];
+  const uint32_t n = d == 0 ? P.n_paths : min(B.counters[QB_CNT_PATHS + d], B.capacity);
   const int bounce_count = P.max_bounce - d;
   const int lane = threadIdx.x & 31;
   const uint32_t lt_mask = (1u << lane) - 1u;
@@ -381,6 +386,10 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade(const DScene S, const WfB
   }
 }
 
+}  // namespace qb
+#include "shade_alt.cuh"
+namespace qb {
+
 // ---- resolve ---------------------------------------------------------------------------------------------------------
 __device__ __forceinline__ float linear_to_srgb(float c)  // renderer.cpp:34-39
 {
@@ -431,6 +440,13 @@ static int persistent_grid_shade()
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void *) k_wf_shade, QB_BLOCK, 0);
+  int alt = 0;  // one grid size for every class: the smallest residency (a persistent grid must be fully resident)
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&alt, (const void *) k_wf_shade_alt<QG_CLASS_MONTECARLOGI, false>, QB_BLOCK, 0);
+  if (alt >= 1 && alt < per_sm) per_sm = alt;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&alt, (const void *) k_wf_shade_alt<QG_CLASS_BLINN_BASIC, false>, QB_BLOCK, 0);
+  if (alt >= 1 && alt < per_sm) per_sm = alt;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&alt, (const void *) k_wf_shade_alt<QG_CLASS_PATHTRACING, false>, QB_BLOCK, 0);
+  if (alt >= 1 && alt < per_sm) per_sm = alt;
   if (per_sm < 1) per_sm = 1;
   return sms * per_sm;
 }
@@ -438,7 +454,14 @@ int wf_shade_grid() { static int g = persistent_grid_shade(); return g; }
 
 void launch_wf_shade(const DScene &S, const WfBuffers &B, const WfParams &P, int grid, cudaStream_t st)
 {
-  k_wf_shade<<<grid, QB_BLOCK, 0, st>>>(S, B, P);
+#define ALT(C) (P.depth == 0 ? k_wf_shade_alt<C, true><<<grid, QB_BLOCK, 0, st>>>(S, B, P) : k_wf_shade_alt<C, false><<<grid, QB_BLOCK, 0, st>>>(S, B, P))
+  switch (P.mtl_class) {
+    case QG_CLASS_PATHTRACING: ALT(QG_CLASS_PATHTRACING); break;
+    case QG_CLASS_MONTECARLOGI: ALT(QG_CLASS_MONTECARLOGI); break;
+    case QG_CLASS_BLINN_BASIC: ALT(QG_CLASS_BLINN_BASIC); break;
+    case QG_CLASS_PHONG_BASIC: ALT(QG_CLASS_PHONG_BASIC); break;
+    default: k_wf_shade<<<grid, QB_BLOCK, 0, st>>>(S, B, P); break;
+  }
 }
 void launch_resolve(const float *accum, const float *depth_in, int n, int spp, int srgb, float *rgb_mean, uint8_t *rgb8, float *depth_out,
                     uint8_t *sample_count, uint8_t *mask, cudaStream_t st)

@@ -328,6 +328,30 @@ __device__ __forceinline__ bool hit_texture(const DScene &S, const DNode *__rest
   return true;
 }
 
+// Hit distances of the two differential rays on the accepted primitive's tangent plane (what IntersectRay stores in
+// DiffHitInfo::x.z / y.z when ray.hasDiffRay): the Whitted-style material classes continue their differential rays from
+// ray.x.p + ray.x.dir * hInfo.x.z (MtlBlinn_Basic.cpp:45-46). rc/rx/ry in the node's space.
+__device__ __forceinline__ void diff_hit_t(const DScene &S, const DNode *__restrict__ n, int slot, float t, const Ray3 &rc, const Ray3 &rx,
+                                           const Ray3 &ry, float &t_x, float &t_y)
+{
+  const int type = __ldg(&n->type);
+  if (type == QG_OBJ_SPHERE) {
+    const V3 p = rc.p + rc.d * t;
+    const V3 N = normalize(p);
+    t_x = -dot(rx.p - p, N) / dot(rx.d, N);
+    t_y = -dot(ry.p - p, N) / dot(ry.d, N);
+  } else if (type == QG_OBJ_PLANE) {
+    t_x = -rx.p.z / rx.d.z;
+    t_y = -ry.p.z / ry.d.z;
+  } else {
+    const DTri *tp = &S.tris[slot];
+    const float4 ta = __ldg(&tp->a), tb = __ldg(&tp->b), tc = __ldg(&tp->c);
+    const V3 A = xyz(ta), N = v3(ta.w, tb.w, tc.w);
+    t_x = -dot(rx.p - A, N) / dot(rx.d, N);
+    t_y = -dot(ry.p - A, N) / dot(ry.d, N);
+  }
+}
+
 // Geometric part of the final hit (p, N, front, mtlID, face) in node space, then FromNodeCoords up to the root.
 __device__ __forceinline__ void hit_geometry(const DScene &S, int k, const DNode *__restrict__ n, int slot, float t, const Ray3 &rc,
                                              HitAttr &h)

@@ -117,7 +117,7 @@ __global__ void __launch_bounds__(QB_BLOCK, QB_MIN_BLOCKS) k_wf_trace(const DSce
 {
   __shared__ uint32_t s_stack[QB_STACK * QB_BLOCK];
   TraceCounters cnt = {0, 0, 0};
-  WfClosestIO<PRIMARY> io{B, P, PRIMARY ? P.n_paths : B.counters[QB_CNT_PATHS + P.depth]};
+  WfClosestIO<PRIMARY> io{B, P, PRIMARY ? P.n_paths : min(B.counters[QB_CNT_PATHS + P.depth], B.capacity)};
   traverse_pool<false>(S, io, s_stack, cnt);
   flush_counters(B.stats, cnt);
 }
@@ -126,9 +126,10 @@ __global__ void __launch_bounds__(QB_BLOCK, QB_MIN_BLOCKS) k_wf_trace(const DSce
 template <bool PRIMARY>
 __global__ void __launch_bounds__(QB_BLOCK) k_wf_finish(const DScene S, const WfBuffers B, const WfParams P)
 {
-  const uint32_t n = PRIMARY ? P.n_paths : B.counters[QB_CNT_PATHS + P.depth];
+  const uint32_t n = PRIMARY ? P.n_paths : min(B.counters[QB_CNT_PATHS + P.depth], B.capacity);
   for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += gridDim.x * blockDim.x) {
     Ray3 c, x, y;
+    bool with_diff = PRIMARY;
     if (PRIMARY) {
       int i, j, s, slot;
       if (!wf_decode(P, idx, i, j, s, slot)) continue;  // h0 already marks the padding lane
@@ -139,6 +140,15 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_finish(const DScene S, const Wf
       c.d = v3(a.w, b.x, b.y);
       x = c;
       y = c;
+      // Whitted-style classes: the secondary ray is DiffRay(p, dir, px, dxdir, py, dydir) (MtlBlinn_Basic.cpp:131,150)
+      if (P.carry_diff && (__float_as_uint(B.ps2[P.depth & 1][idx].w) & QB_FLAG_HAS_DIFF)) {
+        const float4 e = B.ps4[P.depth & 1][idx], f = B.ps5[P.depth & 1][idx], g = B.ps6[P.depth & 1][idx];
+        x.p = v3(e.x, e.y, e.z);
+        x.d = v3(e.w, f.x, f.y);
+        y.p = v3(f.z, f.w, g.x);
+        y.d = v3(g.y, g.z, g.w);
+        with_diff = true;
+      }
     }
     const HitRec rec = get_rec(B.h1, B.h2, idx);
     if (rec.k < 0) {
@@ -146,7 +156,9 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_finish(const DScene S, const Wf
       continue;
     }
     HitAttr h;
-    finish_hit(S, rec, c, x, y, PRIMARY, P.stale_tex != 0, h);
+    float txy[2];
+    finish_hit(S, rec, c, x, y, with_diff, P.stale_tex != 0, h, P.carry_diff ? txy : nullptr);
+    if (P.carry_diff) B.h4[idx] = f4(txy[0], txy[1], 0.f, 0.f);
     const int flags = (h.front ? 1 : 0) | (h.has_texture ? 2 : 0);
     B.h0[idx] = f4(rec.z, __int_as_float(S.obj_node[rec.k]), __int_as_float(h.mtl_id), __int_as_float(flags));
     B.h1[idx] = f4(h.p.x, h.p.y, h.p.z, h.N.x);
@@ -159,7 +171,7 @@ __global__ void __launch_bounds__(QB_BLOCK, QB_MIN_BLOCKS) k_wf_shadow(const DSc
 {
   __shared__ uint32_t s_stack[QB_STACK * QB_BLOCK];
   TraceCounters cnt = {0, 0, 0};
-  WfShadowIO io{B, P, B.counters[QB_CNT_SHADOW + P.depth]};
+  WfShadowIO io{B, P, min(B.counters[QB_CNT_SHADOW + P.depth], B.shadow_capacity)};
   traverse_pool<true>(S, io, s_stack, cnt);
   flush_counters(B.stats, cnt, 5);
 }

@@ -234,7 +234,7 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
 // Attributes of a finished closest-hit ray (what Scene::TraceNodeNormal leaves in DiffHitInfo::c): the tail of
 // trace_closest, run by full warps after the traversal. c/x/y world-space rays as in trace_closest.
 __device__ __forceinline__ void finish_hit(const DScene &S, const HitRec &rec, const Ray3 &c, const Ray3 &x, const Ray3 &y, bool with_diff,
-                                           bool stale_tex, HitAttr &h)
+                                           bool stale_tex, HitAttr &h, float *txy = nullptr)
 {
   const DNode *root = &S.nodes[0];
   const Ray3 c0 = to_node(root, c);
@@ -242,6 +242,10 @@ __device__ __forceinline__ void finish_hit(const DScene &S, const HitRec &rec, c
   const DNode *n = &S.nodes[__ldg(&S.obj_node[best_k])];
   const Ray3 r = chain_ray(S, best_k, c0);
   hit_geometry(S, best_k, n, best_slot, rec.z, r, h);
+  if (txy) {  // DiffHitInfo::x.z / y.z of the accepted hit (objects.cpp:113-131,180-196,264-296)
+    txy[0] = txy[1] = rec.z;
+    if (with_diff) diff_hit_t(S, n, best_slot, rec.z, r, chain_ray(S, best_k, to_node(root, x)), chain_ray(S, best_k, to_node(root, y)), txy[0], txy[1]);
+  }
   if (best_slot < 0 && rec.last_tri >= 0 && stale_tex)
     h.mtl_id = (__ldg(&S.faces[__ldg(&S.tri_face[rec.last_tri]) & 0x7FFFFFFFu].mtl_uv) >> 1) - 1;
   h.uvw = v3(0.5f, 0.5f, 0.5f);

@@ -17,6 +17,10 @@ namespace qb {
 
 #define QB_MAX_BOUNCE 15  // depth slots in the counter block
 
+// path flags (low 8 bits of ps2.w)
+#define QB_FLAG_DIFFUSE_HIT 1u  // HitInfo::hasDiffuseHit of MtlBlinn_PhotonMap
+#define QB_FLAG_HAS_DIFF 2u     // DiffRay::hasDiffRay: ps4..ps6 hold this path's differential rays
+
 // device counter block (uint32 each), zeroed at wave start
 //   [0 .. 15]   n_paths[d]    paths queued for depth d (d >= 1; depth 0 uses the wave size)
 //   [16 .. 31]  n_shadow[d]   shadow rays queued by shade(d)
@@ -34,11 +38,17 @@ struct WfBuffers {
   float4 *ps1[2];  // dir.yz, accum slot (int bits), rng key (uint bits)
   float4 *ps2[2];  // throughput.rgb, packed (rng counter << 8 | flags)
   float4 *ps3[2];  // absorption.rgb of the medium behind the spawning surface, unused
+  // differential rays of secondary paths — only the Whitted-style material classes carry them (MtlBlinn_Basic.cpp:131,
+  // MtlBlinn_MonteCarloGI.cpp:132); null for the path-tracing classes, whose secondary rays are DiffRay(p, dir)
+  float4 *ps4[2];  // x.p.xyz, x.dir.x
+  float4 *ps5[2];  // x.dir.yz, y.p.xy
+  float4 *ps6[2];  // y.p.z, y.dir.xyz
   // hit records written by trace_closest(d), read by shade(d)
   float4 *h0;  // t, object node (int, -1 miss), mtl_id (int), flags (front | has_texture << 1)
   float4 *h1;  // p.xyz, N.x
   float4 *h2;  // N.yz, u, v
   float4 *h3;  // du0, dv0, du1, dv1
+  float4 *h4;  // DiffHitInfo x.z, y.z (hit distances of the differential rays); allocated with ps4..ps6
   // shadow queue
   float4 *s0;  // origin.xyz, dir.x
   float4 *s1;  // dir.yz, tmax, accum slot (int bits)
@@ -64,6 +74,9 @@ struct WfParams {
   int32_t max_bounce;
   int32_t depth;             // current depth d
   int32_t stale_tex;
+  int32_t mtl_class;         // QG_CLASS_*: which of the reference's MtlBlinn classes shades (materials.h:57-61)
+  int32_t carry_diff;        // secondary paths carry differential rays (ps4..ps6 / h4 allocated)
+  int32_t no_falloff;        // DisableInverseSquareFalloff() was called (MtlBlinn_Basic.cpp:18, lights.cpp:21-30)
   float *accum;              // float4 per slot: sum r,g,b, weight
   float *depth_plane;        // may be null
 };

@@ -29,6 +29,7 @@ class RendererParam(object):
         self.height = 0
         self.batch_paths = 0
         self.sort_by_material = 0
+        self.material_class = 0  # QG_CLASS_*: the class the reference's `using MtlBlinn = ...` alias selects (materials.h:57-61)
 
     def SetSPPMin(self, n):
         self.sppMin = int(n)
@@ -44,7 +45,7 @@ class RendererParam(object):
             raise ValueError("adaptive sampling (sppMin < sppMax) is not on the GPU path; use a fixed spp like `-spp N`")
         return capi.RenderParams(self.sppMax, self.maxBounce, int(self.useSRGB), self.seed & 0xFFFFFFFF, self.width,
                                  self.height, tile_rank, tile_ranks, sample_begin, sample_end, self.batch_paths,
-                                 self.sort_by_material)
+                                 self.sort_by_material, self.material_class)
 
 
 def _ptr(a):

@@ -21,7 +21,21 @@ def pytest_configure(config):
 def golden_names():
     if not os.path.isdir(GOLDEN_DIR):
         return []
-    return sorted(f[:-4] for f in os.listdir(GOLDEN_DIR) if f.endswith(".npz") and not f.startswith("img_"))
+    return sorted(f[:-4] for f in os.listdir(GOLDEN_DIR) if f.endswith(".npz") and not f.startswith(("img_", "cls_")))
+
+
+CLASS_ID = {"pathtracing": 1, "montecarlogi": 2, "blinn_basic": 3, "phong_basic": 4}  # QG_CLASS_* (include/qaray_b200.h)
+
+
+def class_golden_cases():
+    """material-class fixtures (tools/make_class_golden.py): cls_<class>_<scene>.npz -> [(class, scene)]"""
+    out = []
+    if os.path.isdir(GOLDEN_DIR):
+        for f in sorted(os.listdir(GOLDEN_DIR)):
+            for cls in CLASS_ID:
+                if f.startswith("cls_%s_" % cls) and f.endswith(".npz"):
+                    out.append((cls, f[len("cls_%s_" % cls):-4]))
+    return out
 
 
 def image_golden_names():
