@@ -142,7 +142,7 @@ typedef struct qgHit {
 } qgHit;
 
 typedef struct qgRenderParams {
-  int32_t spp;         /* RendererParam sppMin = sppMax (src/renderers/renderer.h:47-68, main.cpp:21-24) */
+  int32_t spp;         /* RendererParam::sppMax (src/renderers/renderer.h:47-68); `-spp N` sets min = max (main.cpp:21-24) */
   int32_t max_bounce;  /* Material::maxBounce (src/core/material.cpp:31), default 5 */
   int32_t srgb;        /* RendererParam::useSRGB */
   uint32_t seed;       /* stream seed of the counter-based RNG that replaces src/samplers */
@@ -153,6 +153,8 @@ typedef struct qgRenderParams {
   int32_t sort_by_material; /* reserved, must be 0 */
   int32_t material_class; /* QG_CLASS_*: which MtlBlinn class shades `blinn` materials (the reference picks it with a
                              compile-time alias, src/materials/materials.h:57-61); 0 = MtlBlinn_PhotonMap, its default */
+  int32_t spp_min; /* RendererParam::sppMin when below spp (= sppMax): SuperSamplerHalton's adaptive stop
+                      (src/scene/scene.cpp:92-97); 0 or spp = fixed sample count */
 } qgRenderParams;
 
 typedef struct qgRenderStats {

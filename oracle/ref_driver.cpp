@@ -69,6 +69,9 @@ class HeadlessRenderer : public Renderer {
   const Point3 &U() const { return screenU; }
   const Point3 &V() const { return screenV; }
   const Point3 &A() const { return screenA; }
+  const Point3 &SX() const { return screenX; }
+  const Point3 &SY() const { return screenY; }
+  float Dof() const { return dof; }
   size_t W() const { return pixelW; }
   size_t H() const { return pixelH; }
 };
@@ -196,7 +199,7 @@ void qaref_screen(float *out)
   out[6] = A.x; out[7] = A.y; out[8] = A.z;
 }
 
-// primary DiffRay of pixel (i,j), sample s, exactly as PixelRender builds it (renderer.cpp:312-326, no DOF)
+// primary DiffRay of pixel (i,j), sample s, exactly as PixelRender builds it (renderer.cpp:312-326)
 static DiffRay PrimaryRay(int i, int j, int s, Point3 *texposOut)
 {
   const Point3 texpos = Point3(Halton(s, 11), Halton(s, 13), 0.f) + Point3(i, j, 0.f);
@@ -205,6 +208,11 @@ static DiffRay PrimaryRay(int i, int j, int s, Point3 *texposOut)
   const Point3 xpt = A + (texpos.x + DiffRay::dx) * U + texpos.y * V;
   const Point3 ypt = A + texpos.x * U + (texpos.y + DiffRay::dy) * V;
   Point3 campos = scene.camera.pos;
+  if (g_renderer->Dof() > 0.1f) {  // lens sample (renderer.cpp:319-322): the sample's first two random numbers
+    SuperSamplerHalton lens(Color3f(0.f), 1, 1);
+    const Point3 dofSample = lens.NewDofSample(g_renderer->Dof());
+    campos += dofSample.x * g_renderer->SX() + dofSample.y * g_renderer->SY();
+  }
   DiffRay ray(campos, cpt - campos, campos, xpt - campos, campos, ypt - campos);
   ray.Normalize();
   if (texposOut) *texposOut = texpos;
@@ -336,7 +344,12 @@ void qaref_samples(int64_t n, const int32_t *pix, uint32_t seed, float *rgb, flo
 // Serial fp32 render in the reference's own pixel order (tiles of 4x4 in k order, pixels in idx order,
 // renderer.cpp:387-403) with the reference's running mean (scene.cpp:113-121); fixed spp.
 // rgb: W*H*3 linear means. Used to pin the restatement bit-for-bit (same seed, same draw order).
-void qaref_render_linear_serial(int spp, float *rgb, float *depth)
+void qaref_render_adaptive_serial(int sppMin, int sppMax, float *rgb, float *depth, int32_t *count);
+void qaref_render_linear_serial(int spp, float *rgb, float *depth) { qaref_render_adaptive_serial(spp, spp, rgb, depth, nullptr); }
+
+// PixelRender's loop (renderer.cpp:304-346) with the reference's SuperSamplerHalton, serial, linear output:
+// mean colour, depth of sample 0 and the number of samples each pixel took (sppMin < sppMax = the adaptive stop).
+void qaref_render_adaptive_serial(int sppMin, int sppMax, float *rgb, float *depth, int32_t *count)
 {
   const int W = (int) g_renderer->W(), H = (int) g_renderer->H();
   const int ts = 4;
@@ -349,7 +362,7 @@ void qaref_render_linear_serial(int spp, float *rgb, float *depth)
     for (int idx = 0; idx < np; ++idx) {
       const int j = j0 + idx / (i1 - i0);
       const int i = i0 + idx % (i1 - i0);
-      SuperSamplerHalton sampler(Color3f(0.005f, 0.001f, 0.005f), spp, spp);
+      SuperSamplerHalton sampler(Color3f(0.005f, 0.001f, 0.005f), sppMin, sppMax);
       float d = 0.f;
       while (sampler.Loop()) {
         float c[3], z;
@@ -363,6 +376,7 @@ void qaref_render_linear_serial(int spp, float *rgb, float *depth)
       rgb[3 * (j * W + i) + 1] = m.g;
       rgb[3 * (j * W + i) + 2] = m.b;
       if (depth) depth[j * W + i] = d;
+      if (count) count[j * W + i] = sampler.GetSampleID();
     }
   }
 }

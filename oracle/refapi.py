@@ -146,6 +146,16 @@ class Ref:
         self.lib.qaref_render_linear_serial(int(spp), rgb.ctypes.data_as(C.c_void_p), depth.ctypes.data_as(C.c_void_p))
         return rgb, depth
 
+    def render_adaptive_serial(self, spp_min, spp_max):
+        """PixelRender's loop with SuperSamplerHalton(sppMin, sppMax): linear means, depth, samples taken per pixel"""
+        rgb = np.zeros((self.H, self.W, 3), np.float32)
+        depth = np.zeros((self.H, self.W), np.float32)
+        count = np.zeros((self.H, self.W), np.int32)
+        self.lib.qaref_render_adaptive_serial.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
+        self.lib.qaref_render_adaptive_serial(int(spp_min), int(spp_max), rgb.ctypes.data_as(C.c_void_p),
+                                              depth.ctypes.data_as(C.c_void_p), count.ctypes.data_as(C.c_void_p))
+        return rgb, depth, count
+
     def render(self):
         """The reference's real ThreadRender. Returns (rgb8, depth, sampleCount, seconds)."""
         rgb8 = np.zeros((self.H, self.W, 3), np.uint8)

@@ -72,7 +72,7 @@ class SceneDesc(C.Structure):
 class RenderParams(C.Structure):
     _fields_ = [("spp", i32), ("max_bounce", i32), ("srgb", i32), ("seed", u32), ("width", i32), ("height", i32),
                 ("tile_rank", i32), ("tile_ranks", i32), ("sample_begin", i32), ("sample_end", i32), ("batch_paths", i32),
-                ("sort_by_material", i32), ("material_class", i32)]
+                ("sort_by_material", i32), ("material_class", i32), ("spp_min", i32)]
 
 
 class RenderStats(C.Structure):

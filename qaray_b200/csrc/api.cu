@@ -95,6 +95,7 @@ struct qgScene {
   WfBuffers wf;
   std::vector<void *> wf_allocs;
   uint32_t wf_capacity = 0;
+  int dev_num_area = 0;  // PointLight / SpotLight with size > 0.01 (lights.cpp:52,87)
   DevBuf<unsigned long long> stats;
   cudaStream_t stream = nullptr;
   std::vector<cudaEvent_t> ev_pool;  // timestamp events of KernelClock
@@ -351,6 +352,9 @@ int upload_scene(qgScene *sc)
   D.materials = sc->materials.p; D.multi = sc->multi.p; D.lights = sc->lights.p; D.textures = sc->textures.p; D.texels = sc->texels.p;
   D.num_nodes = nn; D.num_obj = sc->num_obj; D.num_meshes = (int) meshes.size(); D.num_materials = (int) mats.size();
   D.num_lights = (int) lights.size(); D.num_textures = (int) texs.size(); D.num_nonambient = nonambient;
+  sc->dev_num_area = 0;
+  for (const qgLight &l : F.lights)
+    if ((l.type == QG_LIGHT_POINT || l.type == QG_LIGHT_SPOT) && l.size > 0.01f) sc->dev_num_area++;
   put_texcolor_dev(F.background, &D.background);
   put_texcolor_dev(F.environment, &D.environment);
   // Texture::Sample's tap table (core/texture.cpp:38-49): Halton(2,3) points mapped onto the unit-diameter disc
@@ -410,6 +414,16 @@ int ensure_wf(qgScene *sc, uint32_t capacity, bool carry_diff = false)
   CU(alloc4(&B.s0, shadow_cap));
   CU(alloc4(&B.s1, shadow_cap));
   CU(alloc4(&B.s2, shadow_cap));
+  if (sc->dev_num_area > 0) {  // area-light groups: one per (path, area light)
+    const size_t area_cap = std::min<size_t>((size_t) capacity * (size_t) sc->dev_num_area, 0xFFFFFFFFull / QB_AREA_SPP_MAX);
+    CU(alloc4(&B.a0, area_cap));
+    CU(alloc4(&B.a1, area_cap));
+    CU(alloc4(&B.a2, area_cap));
+    CU(cudaMalloc((void **) &B.amask, area_cap * 2 * sizeof(uint32_t)));
+    sc->wf_allocs.push_back(B.amask);
+    CU(cudaMemset(B.amask, 0, area_cap * 2 * sizeof(uint32_t)));
+    B.area_capacity = (uint32_t) area_cap;
+  }
   CU(cudaMalloc((void **) &B.counters, QB_CNT_WORDS * sizeof(uint32_t)));
   sc->wf_allocs.push_back(B.counters);
   B.stats = sc->stats.p;
@@ -420,7 +434,7 @@ int ensure_wf(qgScene *sc, uint32_t capacity, bool carry_diff = false)
 }
 
 // Renderer::ComputeScene's camera frame (renderer.cpp:77-91)
-void camera_frame(const qgCamera &cam, int W, int H, V3 *U, V3 *Vv, V3 *A)
+void camera_frame(const qgCamera &cam, int W, int H, V3 *U, V3 *Vv, V3 *A, V3 *Xo = nullptr, V3 *Yo = nullptr)
 {
   const float PI = (float) M_PI;
   const V3 pos = v3(cam.pos[0], cam.pos[1], cam.pos[2]), dir = v3(cam.dir[0], cam.dir[1], cam.dir[2]), up = v3(cam.up[0], cam.up[1], cam.up[2]);
@@ -434,6 +448,8 @@ void camera_frame(const qgCamera &cam, int W, int H, V3 *U, V3 *Vv, V3 *A)
   *U = X * (screenW / W);
   *Vv = -Y * (screenH / H);
   *A = pos - Z * focal + Y * screenH / 2.f - X * screenW / 2.f;
+  if (Xo) *Xo = X;  // screenX / screenY: the lens plane of the depth-of-field jitter (renderer.cpp:88-89,319-322)
+  if (Yo) *Yo = Y;
 }
 
 bool class_carries_diff(int cls) { return cls == QG_CLASS_MONTECARLOGI || cls == QG_CLASS_BLINN_BASIC || cls == QG_CLASS_PHONG_BASIC; }
@@ -456,7 +472,8 @@ int make_params(const qgScene *sc, const qgRenderParams *rp, WfParams *P, Shard 
   if (s0 == 0 && s1 == 0) s1 = rp->spp;
   if (s0 < 0 || s1 > rp->spp || s0 > s1) return fail(QG_EINVAL, "sample shard out of range");
   memset(P, 0, sizeof *P);
-  camera_frame(cam, W, H, &P->scr_u, &P->scr_v, &P->scr_a);
+  camera_frame(cam, W, H, &P->scr_u, &P->scr_v, &P->scr_a, &P->scr_x, &P->scr_y);
+  P->dof = cam.dof;
   P->cam_pos = v3(cam.pos[0], cam.pos[1], cam.pos[2]);
   P->width = W;
   P->height = H;
@@ -557,14 +574,22 @@ void run_wave(qgScene *sc, WfParams P, cudaStream_t st, uint64_t *launches, Kern
       if (clk) clk->stamp(2);
       *launches += 1;
     }
+    if (sc->dev_num_area > 0) {
+      launch_wf_area(sc->dev, B, P, gsh, st);
+      if (clk) clk->stamp(2);
+      *launches += 2;
+    }
   }
   launch_wf_stats(B, P.max_bounce, st);
   if (clk) clk->stamp(3);
   *launches += 1;
 }
 
+int render_adaptive(qgScene *sc, const qgRenderParams *rp, float *d_accum, float *d_depth, cudaStream_t st, qgRenderStats *stats);
+
 int render_accumulate(qgScene *sc, const qgRenderParams *rp, float *d_accum, float *d_depth, cudaStream_t st, qgRenderStats *stats)
 {
+  if (rp && rp->spp_min > 0 && rp->spp_min < rp->spp) return render_adaptive(sc, rp, d_accum, d_depth, st, stats);
   WfParams P;
   Shard sh;
   int rc = make_params(sc, rp, &P, &sh);
@@ -574,7 +599,8 @@ int render_accumulate(qgScene *sc, const qgRenderParams *rp, float *d_accum, flo
   // shadow-queue state (12 + 3 * lights float4 per path), at most 2^26 paths.
   uint32_t cap = (uint32_t) rp->batch_paths;
   if (rp->batch_paths <= 0) {
-    const unsigned long long per_path = 16ull * ((P.carry_diff ? 19ull : 12ull) + 3ull * (unsigned long long) std::max(1, sc->dev.num_nonambient));
+    const unsigned long long per_path = 16ull * ((P.carry_diff ? 19ull : 12ull) + 3ull * (unsigned long long) std::max(1, sc->dev.num_nonambient)) +
+                                        56ull * (unsigned long long) sc->dev_num_area;
     cap = (uint32_t) std::min<unsigned long long>(1ull << 26, (16ull << 30) / per_path);
   }
   cap = (cap + 31u) & ~31u;
@@ -625,6 +651,109 @@ int render_accumulate(qgScene *sc, const qgRenderParams *rp, float *d_accum, flo
     stats->trace_ms = cms[0];
     stats->shade_ms = cms[1];
     stats->shadow_ms = cms[2];
+  }
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  return QG_OK;
+}
+
+// Renderer::PixelRender with sppMin < sppMax: SuperSamplerHalton's variance-driven stop (src/scene/scene.cpp:92-97).
+// Per round: the pixels still running get their next `chunk` samples as mode-1 paths (radiance kept per path), then
+// k_adaptive_update replays Accumulate / Loop over them in sample order. One host read of the active count per round.
+int render_adaptive(qgScene *sc, const qgRenderParams *rp, float *d_accum, float *d_depth, cudaStream_t st, qgRenderStats *stats)
+{
+  WfParams P;
+  Shard sh;
+  qgRenderParams q = *rp;
+  if (q.sample_begin != 0 || q.sample_end != 0) return fail(QG_EINVAL, "adaptive sampling does not shard by sample index (its stop depends on all earlier samples)");
+  int rc = make_params(sc, &q, &P, &sh);
+  if (rc) return rc;
+  const int W = sh.W, H = sh.H, npix = W * H, spp_min = rp->spp_min, spp_max = rp->spp;
+  const unsigned long long growth = class_growth(P.mtl_class, P.max_bounce);
+  // paths per round: bounded by 2^24 (radiance + triples + wave state stay around a GiB)
+  const unsigned long long round_cap = std::max<unsigned long long>(1ull << 16, (1ull << 24) / growth);
+  DevBuf<int32_t> d_count, d_list, d_trip;
+  DevBuf<uint8_t> d_active;
+  DevBuf<float> d_mean, d_sdev, d_rad, d_rdepth;
+  DevBuf<uint32_t> d_nact;
+  CU(d_count.alloc(npix));
+  CU(d_active.alloc(npix));
+  CU(d_list.alloc(npix));
+  CU(d_mean.alloc(4 * (size_t) npix));
+  CU(d_sdev.alloc(4 * (size_t) npix));
+  CU(d_nact.alloc(1));
+  CU(cudaMemsetAsync(d_count.p, 0, d_count.bytes(), st));
+  CU(cudaMemsetAsync(d_active.p, 1, d_active.bytes(), st));
+  CU(cudaMemsetAsync(d_mean.p, 0, d_mean.bytes(), st));
+  CU(cudaMemsetAsync(d_sdev.p, 0, d_sdev.bytes(), st));
+  CU(cudaMemsetAsync(sc->stats.p, 0, sc->stats.bytes(), st));
+  cudaEvent_t e0, e1;
+  CU(cudaEventCreate(&e0));
+  CU(cudaEventCreate(&e1));
+  CU(cudaEventRecord(e0, st));
+  uint64_t launches = 0, traced = 0;
+  KernelClock clk{sc, st, stats != nullptr};
+  P.mode = 1;
+  size_t trip_cap = 0;
+  uint32_t n_active = (uint32_t) sh.valid_samples / (uint32_t) std::max(1, spp_max);  // pixels this shard owns
+  for (int round = 0; n_active > 0; ++round) {
+    // first round: everyone needs sppMin samples; later rounds look 4 samples ahead
+    int chunk = round == 0 ? spp_min : std::min(4, spp_max - spp_min);
+    chunk = (int) std::max<unsigned long long>(1ull, std::min<unsigned long long>((unsigned long long) chunk, round_cap / std::max<uint32_t>(1u, n_active)));
+    const size_t need = (size_t) n_active * (size_t) chunk;
+    if (need > trip_cap) {
+      CU(d_trip.alloc(3 * need));
+      CU(d_rad.alloc(4 * need));
+      CU(d_rdepth.alloc(need));
+      trip_cap = need;
+    }
+    CU(cudaMemsetAsync(d_nact.p, 0, sizeof(uint32_t), st));
+    launch_adaptive_build(W, H, P.tile_rank, P.tile_ranks, d_count.p, d_active.p, chunk, d_nact.p, d_list.p, d_trip.p, st);
+    uint32_t na = 0;
+    CU(cudaMemcpyAsync(&na, d_nact.p, sizeof na, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+    launches += 1;
+    n_active = na;
+    if (na == 0) break;
+    const size_t np = (size_t) na * (size_t) chunk;
+    CU(cudaMemsetAsync(d_rad.p, 0, 4 * np * sizeof(float), st));
+    uint32_t wave = (uint32_t) std::min<unsigned long long>(np, round_cap);
+    wave = (wave + 31u) & ~31u;
+    rc = ensure_wf(sc, (uint32_t) ((unsigned long long) wave * growth), P.carry_diff != 0);
+    if (rc) return rc;
+    for (size_t base = 0; base < np; base += wave) {
+      P.pix_list = d_trip.p + 3 * base;
+      P.accum = d_rad.p + 4 * base;
+      P.depth_plane = d_rdepth.p + base;
+      P.wave_base = 0;
+      P.n_paths = (uint32_t) std::min<size_t>(wave, np - base);
+      run_wave(sc, P, st, &launches, &clk);
+    }
+    traced += np;
+    launch_adaptive_update(na, d_list.p, chunk, d_rad.p, d_rdepth.p, spp_min, spp_max, d_count.p, d_active.p, d_mean.p, d_sdev.p, d_depth, st);
+    launches += 1;
+  }
+  launch_adaptive_finish(npix, d_count.p, d_mean.p, d_accum, st);
+  launches += 1;
+  CU(cudaEventRecord(e1, st));
+  CU(cudaStreamSynchronize(st));
+  CU(cudaGetLastError());
+  if (stats) {
+    unsigned long long hs[8];
+    CU(cudaMemcpy(hs, sc->stats.p, sizeof hs, cudaMemcpyDeviceToHost));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    memset(stats, 0, sizeof *stats);
+    stats->samples = traced;  // samples traced, including look-ahead samples the stop rule then discarded
+    stats->closest_rays = hs[0] + traced;
+    stats->shadow_rays = hs[1];
+    stats->nodes_visited = hs[2]; stats->tris_tested = hs[3]; stats->objects_tested = hs[4];
+    stats->shadow_nodes_visited = hs[5]; stats->shadow_tris_tested = hs[6]; stats->shadow_objects_tested = hs[7];
+    stats->kernel_launches = launches;
+    stats->device_ms = ms;
+    double cms[4];
+    clk.sums(cms);
+    stats->trace_ms = cms[0]; stats->shade_ms = cms[1]; stats->shadow_ms = cms[2];
   }
   cudaEventDestroy(e0);
   cudaEventDestroy(e1);

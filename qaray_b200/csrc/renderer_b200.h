@@ -90,10 +90,6 @@ class Renderer_B200 {
   bool Render()
   {
     if (param.usePhotonMap) { fprintf(stderr, "Renderer_B200: -use-photon-map is not on the GPU path\n"); return false; }
-    if (param.sppMin != param.sppMax) {
-      fprintf(stderr, "Renderer_B200: adaptive sampling (sppMin != sppMax) is not on the GPU path; use -spp N\n");
-      return false;
-    }
     qgRenderParams rp{};
     rp.spp = (int32_t) param.sppMax;
     rp.max_bounce = param.maxBounce;
@@ -104,6 +100,7 @@ class Renderer_B200 {
     rp.tile_rank = (int32_t) mpiRank;
     rp.tile_ranks = (int32_t) mpiSize;
     rp.material_class = param.materialClass;
+    rp.spp_min = param.sppMin < param.sppMax ? (int32_t) param.sppMin : 0;  // SuperSamplerHalton's adaptive stop
     if (qg_render(scene, &rp, linearBuffer.data(), colorBuffer.data(), depthBuffer.data(), sampleCountBuffer.data(), maskBuffer.data(),
                   &stats) != QG_OK) {
       fprintf(stderr, "Renderer_B200::Render: %s\n", qg_last_error());

@@ -26,11 +26,6 @@ struct AltChild {
   uint32_t key, n, flags;
 };
 
-__device__ __forceinline__ uint32_t child_key(uint32_t key, uint32_t n, uint32_t c)
-{
-  return rng_mix(key ^ rng_mix(n * 0x9E3779B9u + c * 0x85EBCA77u + 0x2545F491u));
-}
-
 // warp-converged: every lane calls it; lanes with c.on append one path to the queue of depth d + 1
 __device__ __forceinline__ void push_child(const WfBuffers &B, const WfParams &P, int d, int lane, uint32_t lt_mask, V3 p, int slot,
                                            const AltChild &c)
@@ -127,16 +122,18 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade_alt(const DScene S, const
         valid = wf_decode(P, idx, i, j, s, slot);
         if (valid) {
           rng.key = rng_key((uint32_t) (j * P.width + i), (uint32_t) s, P.seed);
+          rng.n = wf_dof_draws(P);
           atomicAdd(P.accum + 4ll * slot + 3, 1.0f);
           if (P.depth_plane && (s == 0 || P.mode == 1)) P.depth_plane[slot] = node >= 0 ? h0.x : QB_BIGFLOAT;
           const float tx = halton(s, 11) + (float) i, ty = halton(s, 13) + (float) j;
           if (node < 0) {  // background by screen position (renderer.cpp:336-338)
             accum_add(P.accum, slot, texcolor_sample1(S, S.background, v3(tx / (float) P.width, ty / (float) P.height, 0.f)));
           } else {  // the primary DiffRay (renderer.cpp:312-326)
-            rc.p = rx.p = ry.p = P.cam_pos;
-            rc.d = normalize(P.scr_a + tx * P.scr_u + ty * P.scr_v - P.cam_pos);
-            rx.d = normalize(P.scr_a + (tx + 0.01f) * P.scr_u + ty * P.scr_v - P.cam_pos);
-            ry.d = normalize(P.scr_a + tx * P.scr_u + (ty + 0.01f) * P.scr_v - P.cam_pos);
+            const V3 campos = wf_campos(P, i, j, s);
+            rc.p = rx.p = ry.p = campos;
+            rc.d = normalize(P.scr_a + tx * P.scr_u + ty * P.scr_v - campos);
+            rx.d = normalize(P.scr_a + (tx + 0.01f) * P.scr_u + ty * P.scr_v - campos);
+            ry.d = normalize(P.scr_a + tx * P.scr_u + (ty + 0.01f) * P.scr_v - campos);
           }
         }
       } else {
@@ -349,6 +346,7 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade_alt(const DScene S, const
         }
         continue;
       }
+      const bool area = lt.type != QG_LIGHT_DIRECT && lt.size > 0.01f;  // lights.cpp:52,87 (uniform across the warp)
       bool push = false;
       V3 sdir = v3(0.f), contrib = v3(0.f);
       float tmax = QB_BIGFLOAT;
@@ -361,13 +359,17 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade_alt(const DScene S, const
           const V3 dv = ld3(lt.position) - p;
           sdir = normalize(dv);
           tmax = length(dv);
-          if (!P.no_falloff) I = I * qmin(1.f, 1.f / length2(dv));  // InverseSquareFalloff, lights.cpp:23-30
+          if (!P.no_falloff && !area) I = I * qmin(1.f, 1.f / length2(dv));  // InverseSquareFalloff, lights.cpp:23-30
           Ldir = normalize(p - ld3(lt.position));
           if (lt.type == QG_LIGHT_SPOT) I = I * spot_attenuation(lt, Ldir);
         }
         const V3 L = normalize(-Ldir);
         contrib = T * (I * light_factor<CLS>(N, V, L, Kd, Ks, gloss, norm_di));
         push = (contrib.x != 0.f) || (contrib.y != 0.f) || (contrib.z != 0.f);
+      }
+      if (area) {
+        push_area_group(B, d, lane, lt_mask, push, p, l, slot, contrib, child_key(rng.key, rng.n, 0x100u + (uint32_t) l));
+        continue;
       }
       const uint32_t mask = __ballot_sync(0xFFFFFFFFu, push);
       if (mask) {

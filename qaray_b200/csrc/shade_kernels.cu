@@ -175,6 +175,29 @@ __device__ __forceinline__ void accum_add(float *accum, int slot, V3 c)
   atomicAdd(a + 2, c.z);
 }
 
+// stream key of a child path / of an area-light group: (parent key, parent counter, index)
+__device__ __forceinline__ uint32_t child_key(uint32_t key, uint32_t n, uint32_t c)
+{
+  return rng_mix(key ^ rng_mix(n * 0x9E3779B9u + c * 0x85EBCA77u + 0x2545F491u));
+}
+
+// warp-converged: lanes with `push` append one (hit, area light) group; its shadow samples are generated by k_wf_area_*
+__device__ __forceinline__ void push_area_group(const WfBuffers &B, int d, int lane, uint32_t lt_mask, bool push, V3 p, int light, int slot,
+                                                V3 contrib, uint32_t gkey)
+{
+  const uint32_t mask = __ballot_sync(0xFFFFFFFFu, push);
+  if (!mask) return;
+  uint32_t qbase = 0;
+  if (lane == 0) qbase = atomicAdd(&B.counters[QB_CNT_AREA + d], (uint32_t) __popc(mask));
+  qbase = __shfl_sync(0xFFFFFFFFu, qbase, 0);
+  if (!push) return;
+  const uint32_t q = qbase + __popc(mask & lt_mask);
+  if (q >= B.area_capacity) return;
+  B.a0[q] = make_float4(p.x, p.y, p.z, __uint_as_float(gkey));
+  B.a1[q] = make_float4(__int_as_float(light), __int_as_float(slot), 0.f, 0.f);
+  B.a2[q] = make_float4(contrib.x, contrib.y, contrib.z, 0.f);
+}
+
 __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade(const DScene S, const WfBuffers B, const WfParams P)
 {
   const int d = P.depth;
@@ -212,6 +235,7 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade(const DScene S, const WfB
         valid = wf_decode(P, idx, i, j, s, slot);
         if (valid) {
           rng.key = rng_key((uint32_t) (j * P.width + i), (uint32_t) s, P.seed);
+          rng.n = wf_dof_draws(P);
           atomicAdd(P.accum + 4ll * slot + 3, 1.0f);
           if (P.depth_plane && (s == 0 || P.mode == 1)) P.depth_plane[slot] = node >= 0 ? h0.x : QB_BIGFLOAT;
           if (node < 0) {  // background by screen position (renderer.cpp:336-338)
@@ -220,7 +244,7 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade(const DScene S, const WfB
           } else {
             const float tx = halton(s, 11) + (float) i, ty = halton(s, 13) + (float) j;
             const V3 cpt = P.scr_a + tx * P.scr_u + ty * P.scr_v;
-            ray_dir = normalize(cpt - P.cam_pos);
+            ray_dir = normalize(cpt - wf_campos(P, i, j, s));
           }
         }
       } else {
@@ -332,6 +356,7 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade(const DScene S, const WfB
     for (int l = 0; l < S.num_lights; ++l) {
       const DLight &lt = S.lights[l];
       if (lt.type == QG_LIGHT_AMBIENT) continue;  // uniform across the warp
+      const bool area = lt.type != QG_LIGHT_DIRECT && lt.size > 0.01f;  // lights.cpp:52,87 (uniform across the warp)
       bool push = false;
       V3 sdir = v3(0.f), contrib = v3(0.f);
       float tmax = QB_BIGFLOAT;
@@ -344,7 +369,7 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade(const DScene S, const WfB
           const V3 dv = ld3(lt.position) - p;
           sdir = normalize(dv);
           tmax = length(dv);
-          I = I * qmin(1.f, 1.f / length2(dv));  // InverseSquareFalloff
+          if (!area) I = I * qmin(1.f, 1.f / length2(dv));  // InverseSquareFalloff (an area light folds it into its shadow estimate)
           Ldir = normalize(p - ld3(lt.position));
           if (lt.type == QG_LIGHT_SPOT) I = I * spot_attenuation(lt, Ldir);
         }
@@ -353,6 +378,10 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade(const DScene S, const WfB
         const float cosNL = qmax(0.f, dot(N, L)), cosNH = qmax(0.f, dot(N, H));
         contrib = T * ((I * norm_di) * cosNL * (Kd + Ks * powf(cosNH, gloss)));
         push = (contrib.x != 0.f) || (contrib.y != 0.f) || (contrib.z != 0.f);
+      }
+      if (area) {
+        push_area_group(B, d, lane, lt_mask, push, p, l, slot, contrib, child_key(rng.key, rng.n, 0x100u + (uint32_t) l));
+        continue;
       }
       const uint32_t mask = __ballot_sync(0xFFFFFFFFu, push);
       if (mask) {
@@ -421,13 +450,97 @@ __global__ void k_resolve(const float *__restrict__ accum, const float *__restri
   if (mask) mask[i] = w > 0.f ? 1 : 0;
 }
 
+// ---- adaptive sampling: SuperSamplerHalton (src/scene/scene.cpp:83-123) -----------------------------------------------------
+// The reference loops per pixel: sample, Accumulate (running mean + a variance proxy), stop when s >= sppMin and every
+// channel's proxy is below (0.005, 0.001, 0.005), or at sppMax. Sample s of a pixel is a pure function of (pixel, s, seed)
+// here, so pixels still running get their next `chunk` samples traced together (one path each, radiance kept per path),
+// and k_adaptive_update replays the reference's loop over them in order; samples past the stop are discarded unseen.
+__device__ __forceinline__ bool adaptive_loop(int s, V3 sd, int spp_min, int spp_max)  // SuperSamplerHalton::Loop
+{
+  return s < spp_min || (s >= spp_min && s < spp_max && (sd.x > 0.005f || sd.y > 0.001f || sd.z > 0.005f));
+}
+
+// pixels of this tile shard that are still running -> compact list + their next `chunk` (i, j, s) triples
+__global__ void k_adaptive_build(int W, int H, int tile_rank, int tile_ranks, const int32_t *__restrict__ count,
+                                 const uint8_t *__restrict__ active, int chunk, uint32_t *__restrict__ n_active, int32_t *__restrict__ list,
+                                 int32_t *__restrict__ triples)
+{
+  const int pix = blockIdx.x * blockDim.x + threadIdx.x;
+  if (pix >= W * H || !active[pix]) return;
+  const int i = pix % W, j = pix / W;
+  const int tiles_x = (W + 3) / 4;
+  const int k = (j / 4) * tiles_x + (i / 4);  // 4x4 tile index; the shard owns k = rank (mod ranks) (renderer.cpp:383-398)
+  if (k % tile_ranks != tile_rank) return;
+  const uint32_t a = atomicAdd(n_active, 1u);
+  list[a] = pix;
+  const int s0 = count[pix];
+  for (int c = 0; c < chunk; ++c) {
+    int32_t *t = triples + 3ll * ((long long) a * chunk + c);
+    t[0] = i; t[1] = j; t[2] = s0 + c;
+  }
+}
+
+// SuperSamplerHalton::Accumulate over the chunk, in sample order; stops where Loop() stops
+__global__ void k_adaptive_update(uint32_t n_active, const int32_t *__restrict__ list, int chunk, const float4 *__restrict__ rad,
+                                  const float *__restrict__ rad_depth, int spp_min, int spp_max, int32_t *__restrict__ count,
+                                  uint8_t *__restrict__ active, float4 *__restrict__ mean, float4 *__restrict__ sdev, float *__restrict__ depth)
+{
+  const uint32_t a = blockIdx.x * blockDim.x + threadIdx.x;
+  if (a >= n_active) return;
+  const int pix = list[a];
+  int s = count[pix];
+  const float4 m4 = mean[pix], s4 = sdev[pix];
+  V3 color = v3(m4.x, m4.y, m4.z), sd = v3(s4.x, s4.y, s4.z);
+  for (int c = 0; c < chunk && adaptive_loop(s, sd, spp_min, spp_max); ++c) {
+    const float4 r = rad[(long long) a * chunk + c];
+    if (s == 0 && depth) depth[pix] = rad_depth[(long long) a * chunk + c];
+    const V3 dc = (v3(r.x, r.y, r.z) - color) / (float) (s + 1);
+    color += dc;
+    if (s > 0) sd += dc * dc * (float) (s + 1) - sd / (float) s;
+    ++s;
+  }
+  count[pix] = s;
+  mean[pix] = make_float4(color.x, color.y, color.z, 0.f);
+  sdev[pix] = make_float4(sd.x, sd.y, sd.z, 0.f);
+  active[pix] = adaptive_loop(s, sd, spp_min, spp_max) ? 1 : 0;
+}
+
+// mean and sample count -> the {sum, weight} accumulation buffer the resolve step reads
+__global__ void k_adaptive_finish(int n, const int32_t *__restrict__ count, const float4 *__restrict__ mean, float *__restrict__ accum)
+{
+  const int pix = blockIdx.x * blockDim.x + threadIdx.x;
+  if (pix >= n) return;
+  const float w = (float) count[pix];
+  if (w <= 0.f) return;
+  const float4 m = mean[pix];
+  float4 *a = reinterpret_cast<float4 *>(accum) + pix;
+  *a = make_float4(a->x + m.x * w, a->y + m.y * w, a->z + m.z * w, a->w + w);
+}
+
+void launch_adaptive_build(int W, int H, int tile_rank, int tile_ranks, const int32_t *count, const uint8_t *active, int chunk,
+                           uint32_t *n_active, int32_t *list, int32_t *triples, cudaStream_t st)
+{
+  k_adaptive_build<<<(W * H + 255) / 256, 256, 0, st>>>(W, H, tile_rank, tile_ranks, count, active, chunk, n_active, list, triples);
+}
+void launch_adaptive_update(uint32_t n_active, const int32_t *list, int chunk, const float *rad, const float *rad_depth, int spp_min,
+                            int spp_max, int32_t *count, uint8_t *active, float *mean, float *sdev, float *depth, cudaStream_t st)
+{
+  if (n_active == 0) return;
+  k_adaptive_update<<<(n_active + 255) / 256, 256, 0, st>>>(n_active, list, chunk, (const float4 *) rad, rad_depth, spp_min, spp_max, count,
+                                                            active, (float4 *) mean, (float4 *) sdev, depth);
+}
+void launch_adaptive_finish(int n, const int32_t *count, const float *mean, float *accum, cudaStream_t st)
+{
+  k_adaptive_finish<<<(n + 255) / 256, 256, 0, st>>>(n, count, (const float4 *) mean, accum);
+}
+
 // wave epilogue: fold the wave's queue counters into the running ray statistics
 __global__ void k_wf_stats(const uint32_t *__restrict__ counters, unsigned long long *__restrict__ stats, int max_bounce)
 {
   unsigned long long closest = 0, shadow = 0;
   for (int d = 0; d <= max_bounce; ++d) {
     if (d >= 1) closest += counters[QB_CNT_PATHS + d];
-    shadow += counters[QB_CNT_SHADOW + d];
+    shadow += counters[QB_CNT_SHADOW + d] + (unsigned long long) counters[QB_CNT_AREA + d] * QB_AREA_SPP_MAX;
   }
   stats[0] += closest;
   stats[1] += shadow;

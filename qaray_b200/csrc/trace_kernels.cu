@@ -16,7 +16,7 @@ namespace qb {
 
 __device__ __forceinline__ float4 f4(float x, float y, float z, float w) { return make_float4(x, y, z, w); }
 
-// primary DiffRay of pixel (i,j), sample s (no depth of field): texpos = (i + H11(s), j + H13(s))
+// primary DiffRay of pixel (i,j), sample s: texpos = (i + H11(s), j + H13(s)), origin = wf_campos (lens sample with DOF)
 __device__ __forceinline__ void primary_ray(const WfParams &P, int i, int j, int s, Ray3 &c, Ray3 &x, Ray3 &y)
 {
   const float tx = halton(s, 11) + (float) i;
@@ -24,10 +24,11 @@ __device__ __forceinline__ void primary_ray(const WfParams &P, int i, int j, int
   const V3 cpt = P.scr_a + tx * P.scr_u + ty * P.scr_v;
   const V3 xpt = P.scr_a + (tx + 0.01f) * P.scr_u + ty * P.scr_v;
   const V3 ypt = P.scr_a + tx * P.scr_u + (ty + 0.01f) * P.scr_v;
-  c.p = x.p = y.p = P.cam_pos;
-  c.d = normalize(cpt - P.cam_pos);
-  x.d = normalize(xpt - P.cam_pos);
-  y.d = normalize(ypt - P.cam_pos);
+  const V3 campos = wf_campos(P, i, j, s);
+  c.p = x.p = y.p = campos;
+  c.d = normalize(cpt - campos);
+  x.d = normalize(xpt - campos);
+  y.d = normalize(ypt - campos);
 }
 
 // counting build only: stats[2..4] = BVH nodes / triangles / objects visited by closest-hit rays, [5..7] by any-hit rays
@@ -174,6 +175,78 @@ __global__ void __launch_bounds__(QB_BLOCK, QB_MIN_BLOCKS) k_wf_shadow(const DSc
   WfShadowIO io{B, P, min(B.counters[QB_CNT_SHADOW + P.depth], B.shadow_capacity)};
   traverse_pool<true>(S, io, s_stack, cnt);
   flush_counters(B.stats, cnt, 5);
+}
+
+// ---- area lights: PointLight / SpotLight with size > 0.01 (src/lights/lights.cpp:50-65,84-101) -----------------------------
+// The reference estimates such a light's visibility with 16 shadow rays toward `position + UniformBall(size)`, and 64 when
+// the running estimate ever lies strictly between 0 and 1. Sample s of a group is a pure function of (group key, s), so
+// all 64 are traced here (any-hit, results as one bit each) and the resolve step replays the reference's loop over as many
+// of them as it would have drawn — the unused ones change nothing.
+struct WfAreaIO {
+  const DScene &S;
+  const WfBuffers &B;
+  const WfParams &P;
+  uint32_t n;  // QB_AREA_SPP_MAX * groups
+  __device__ uint32_t count() const { return n; }
+  __device__ uint32_t *cursor() { return &B.counters[QB_CNT_FETCH_AREA + P.depth]; }
+  __device__ bool load(uint32_t idx, Ray3 &c, float &tmax)
+  {
+    const uint32_t g = idx / QB_AREA_SPP_MAX;
+    const int s = (int) (idx % QB_AREA_SPP_MAX);
+    const float4 a = B.a0[g];
+    const V3 p = v3(a.x, a.y, a.z);
+    const V3 dir = wf_area_dir(S.lights[__float_as_int(B.a1[g].x)], p, __float_as_uint(a.w), s);
+    c.p = p;
+    c.d = normalize(dir);  // Ray ray(p, dir); ray.Normalize(); Shadow(ray, length(dir))
+    tmax = length(dir);
+    return true;
+  }
+  __device__ void store(uint32_t, const HitRec &) {}
+  __device__ void store_any(uint32_t idx, bool occluded)
+  {
+    if (occluded) return;
+    const uint32_t g = idx / QB_AREA_SPP_MAX, s = idx % QB_AREA_SPP_MAX;
+    atomicOr(&B.amask[2u * g + (s >> 5)], 1u << (s & 31u));
+  }
+};
+
+__global__ void __launch_bounds__(QB_BLOCK, QB_MIN_BLOCKS) k_wf_area_shadow(const DScene S, const WfBuffers B, const WfParams P)
+{
+  __shared__ uint32_t s_stack[QB_STACK * QB_BLOCK];
+  TraceCounters cnt = {0, 0, 0};
+  WfAreaIO io{S, B, P, min(B.counters[QB_CNT_AREA + P.depth], B.area_capacity) * (uint32_t) QB_AREA_SPP_MAX};
+  traverse_pool<true>(S, io, s_stack, cnt);
+  flush_counters(B.stats, cnt, 5);
+}
+
+// PointLight::Illuminate's loop (lights.cpp:53-64) over the traced samples, one thread per group
+__global__ void __launch_bounds__(QB_BLOCK) k_wf_area_resolve(const DScene S, const WfBuffers B, const WfParams P)
+{
+  const uint32_t n = min(B.counters[QB_CNT_AREA + P.depth], B.area_capacity);
+  for (uint32_t g = blockIdx.x * blockDim.x + threadIdx.x; g < n; g += gridDim.x * blockDim.x) {
+    const float4 a = B.a0[g], b = B.a1[g], c = B.a2[g];
+    const V3 p = v3(a.x, a.y, a.z);
+    const DLight &lt = S.lights[__float_as_int(b.x)];
+    const uint32_t m0 = B.amask[2u * g], m1 = B.amask[2u * g + 1u];
+    B.amask[2u * g] = 0u;  // leave the mask clear for the next depth / wave
+    B.amask[2u * g + 1u] = 0u;
+    int spp = QB_AREA_SPP_MIN, s = 0;
+    float inshadow = 0.0f;
+    while (s < spp) {
+      const V3 dir = wf_area_dir(lt, p, __float_as_uint(a.w), s);
+      const float vis = (((s < 32 ? m0 : m1) >> (s & 31)) & 1u) ? 1.0f : 0.0f;
+      const float falloff = P.no_falloff ? 1.f : qmin(1.f, 1.f / length2(dir));  // InverseSquareFalloff (lights.cpp:23-30)
+      inshadow += (vis - inshadow) * falloff / (float) (s + 1);
+      s++;
+      if (inshadow > 0.f && inshadow < 1.f) spp = QB_AREA_SPP_MAX;
+    }
+    if (inshadow != 0.f) {
+      float *acc = P.accum + 4ll * (long long) __float_as_int(b.y);
+      atomicAdd(acc + 0, c.x * inshadow);
+      atomicAdd(acc + 1, c.y * inshadow);
+      atomicAdd(acc + 2, c.z * inshadow);
+    }
+  }
 }
 
 // ---- C-ABI ray-buffer kernels: the same traversal core over caller-supplied rays ----------------------------------------
@@ -323,6 +396,11 @@ void launch_wf_trace(const DScene &S, const WfBuffers &B, const WfParams &P, int
 void launch_wf_shadow(const DScene &S, const WfBuffers &B, const WfParams &P, int grid, cudaStream_t st)
 {
   k_wf_shadow<<<grid, QB_BLOCK, 0, st>>>(S, B, P);
+}
+void launch_wf_area(const DScene &S, const WfBuffers &B, const WfParams &P, int grid, cudaStream_t st)
+{
+  k_wf_area_shadow<<<grid, QB_BLOCK, 0, st>>>(S, B, P);
+  k_wf_area_resolve<<<148 * 8, QB_BLOCK, 0, st>>>(S, B, P);
 }
 static int flat_grid(size_t n)
 {

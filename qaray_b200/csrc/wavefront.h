@@ -30,7 +30,13 @@ namespace qb {
 #define QB_CNT_FETCH_TRACE 32
 #define QB_CNT_FETCH_SHADE 48
 #define QB_CNT_FETCH_SHADOW 64
-#define QB_CNT_WORDS 96
+#define QB_CNT_AREA 80         // [80 .. 95] n_area[d]: (hit, area light) groups queued by shade(d)
+#define QB_CNT_FETCH_AREA 96   // [96 .. 111] work-fetch cursor of the area-light shadow kernel
+#define QB_CNT_WORDS 112
+
+// area lights (PointLight / SpotLight with size > 0.01, src/lights/lights.cpp:50-65,84-101): shadow samples per group
+#define QB_AREA_SPP_MIN 16     // GenLight::shadow_spp_min (lights.cpp:16)
+#define QB_AREA_SPP_MAX 64     // GenLight::shadow_spp_max (lights.cpp:17)
 
 struct WfBuffers {
   // path state, ping-pong by depth parity: [d & 1]
@@ -53,6 +59,12 @@ struct WfBuffers {
   float4 *s0;  // origin.xyz, dir.x
   float4 *s1;  // dir.yz, tmax, accum slot (int bits)
   float4 *s2;  // contribution.rgb if unoccluded
+  // area-light groups: one entry per (shaded hit, area light); its 64 shadow rays are generated on the fly
+  float4 *a0;       // p.xyz, group rng key (uint bits)
+  float4 *a1;       // light index (int bits), accum slot (int bits), unused
+  float4 *a2;       // contribution.rgb per unit of the light's visibility estimate
+  uint32_t *amask;  // 2 words per group: bit s = shadow sample s reached the light
+  uint32_t area_capacity;
   uint32_t *counters;
   unsigned long long *stats;  // [0] closest rays, [1] shadow rays, [2] nodes, [3] tris, [4] objects
   uint32_t capacity;          // paths per wave
@@ -63,6 +75,9 @@ struct WfParams {
   // camera frame (Renderer::ComputeScene, renderer.cpp:77-91)
   V3 cam_pos, scr_u, scr_v, scr_a;
   int32_t width, height;
+  // depth of field (renderer.cpp:319-322): lens radius (active above 0.1) and the camera's X / Y axes
+  float dof;
+  V3 scr_x, scr_y;
   // sample enumeration
   int32_t mode;              // 0: 4x4 tiles k = tile_rank + lt*tile_ranks (renderer.cpp:383-398); 1: explicit (i,j,s) list
   int32_t tiles_x, tile_rank, tile_ranks, tiles_local;
@@ -104,11 +119,50 @@ __host__ __device__ inline bool wf_decode(const WfParams &P, uint32_t idx, int &
   return i < P.width && j < P.height;
 }
 
+// Ray origin of pixel (i,j), sample s: the camera position, or with depth of field a point on the lens disc drawn with
+// the sample's first two random numbers (SuperSamplerHalton::NewDofSample, src/scene/scene.cpp:104-111).
+// wf_dof_draws = how many numbers of the sample's stream that consumed.
+__host__ __device__ inline uint32_t wf_dof_draws(const WfParams &P) { return P.dof > 0.1f ? 2u : 0u; }
+__host__ __device__ inline V3 wf_campos(const WfParams &P, int i, int j, int s)
+{
+  if (!(P.dof > 0.1f)) return P.cam_pos;
+  const uint32_t key = rng_key((uint32_t) (j * P.width + i), (uint32_t) s, P.seed);
+  const float r1 = rng_float(key, 0u), r2 = rng_float(key, 1u);
+  const float r = P.dof * sqrtf(r1);
+  const float t = r2 * 2.f * 3.14159274101257324f;
+  return P.cam_pos + ((r * cosf(t)) * P.scr_x + (r * sinf(t)) * P.scr_y);
+}
+
+// Shadow sample s of an area-light group: the un-normalised direction `position + UniformBall(size) - p` of
+// PointLight::Illuminate (lights.cpp:54). Every sample has its own counter-based stream keyed by (group key, s), so the
+// shadow kernel and the resolve kernel regenerate the same direction without storing 64 rays per group.
+// Sampler::UniformBall (core/sampler.cpp:42-53): rejection from the cube, z re-uses r2 as the reference does.
+__host__ __device__ inline V3 wf_area_dir(const DLight &lt, V3 p, uint32_t gkey, int s)
+{
+  const uint32_t key = rng_mix(gkey ^ rng_mix((uint32_t) s * 0x9E3779B9u + 0x51ED270Bu));
+  uint32_t n = 0;
+  V3 b = v3(0.f);
+  for (int it = 0; it < 64; ++it) {
+    const float r1 = rng_float(key, n), r2 = rng_float(key, n + 1u);
+    n += 3u;  // Get3f draws three numbers; the third is unused (sampler.cpp:50)
+    b = v3((2.f * r1 - 1.f) * lt.size, (2.f * r2 - 1.f) * lt.size, (2.f * r2 - 1.f) * lt.size);
+    if (!(length(b) > lt.size)) break;
+  }
+  return (v3(lt.position[0], lt.position[1], lt.position[2]) + b) - p;
+}
+
 // launch wrappers (implemented in trace_kernels.cu / shade_kernels.cu)
 void launch_wf_trace(const DScene &S, const WfBuffers &B, const WfParams &P, int grid, cudaStream_t st);
 void launch_wf_shadow(const DScene &S, const WfBuffers &B, const WfParams &P, int grid, cudaStream_t st);
 void launch_wf_shade(const DScene &S, const WfBuffers &B, const WfParams &P, int grid, cudaStream_t st);
+void launch_wf_area(const DScene &S, const WfBuffers &B, const WfParams &P, int grid, cudaStream_t st);  // area shadow rays + resolve
 void launch_wf_stats(const WfBuffers &B, int max_bounce, cudaStream_t st);
+// adaptive sampling (SuperSamplerHalton, src/scene/scene.cpp:83-123), see shade_kernels.cu
+void launch_adaptive_build(int W, int H, int tile_rank, int tile_ranks, const int32_t *count, const uint8_t *active, int chunk,
+                           uint32_t *n_active, int32_t *list, int32_t *triples, cudaStream_t st);
+void launch_adaptive_update(uint32_t n_active, const int32_t *list, int chunk, const float *rad, const float *rad_depth, int spp_min,
+                            int spp_max, int32_t *count, uint8_t *active, float *mean, float *sdev, float *depth, cudaStream_t st);
+void launch_adaptive_finish(int n, const int32_t *count, const float *mean, float *accum, cudaStream_t st);
 void launch_resolve(const float *accum, const float *depth_in, int n, int spp, int srgb, float *rgb_mean, uint8_t *rgb8, float *depth_out,
                     uint8_t *sample_count, uint8_t *mask, cudaStream_t st);
 size_t trace_rays_scratch_bytes(size_t n);  // device scratch the two ray-buffer launchers need

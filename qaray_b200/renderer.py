@@ -41,11 +41,11 @@ class RendererParam(object):
         self.useSRGB = bool(f)
 
     def to_c(self, tile_rank=0, tile_ranks=1, sample_begin=0, sample_end=0):
-        if self.sppMin != self.sppMax:
-            raise ValueError("adaptive sampling (sppMin < sppMax) is not on the GPU path; use a fixed spp like `-spp N`")
+        if self.sppMin > self.sppMax:
+            raise ValueError("sppMin > sppMax")
         return capi.RenderParams(self.sppMax, self.maxBounce, int(self.useSRGB), self.seed & 0xFFFFFFFF, self.width,
                                  self.height, tile_rank, tile_ranks, sample_begin, sample_end, self.batch_paths,
-                                 self.sort_by_material, self.material_class)
+                                 self.sort_by_material, self.material_class, self.sppMin if self.sppMin < self.sppMax else 0)
 
 
 def _ptr(a):

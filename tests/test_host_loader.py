@@ -35,7 +35,7 @@ def test_struct_sizes_match_the_header():
     assert C.sizeof(capi.TexturedColor) == 100
     assert C.sizeof(capi.Light) == 52
     assert C.sizeof(capi.Camera) == 56
-    assert C.sizeof(capi.RenderParams) == 52
+    assert C.sizeof(capi.RenderParams) == 56
     assert capi.RAY_DTYPE.itemsize == 76 and capi.HIT_DTYPE.itemsize == 88
 
 
