@@ -20,8 +20,15 @@ namespace qb {
 #define QB_BIAS 0.005f
 #define QB_MAX_DEPTH 8      // scene-tree depth supported by the chain replay
 #define QB_BLOCK 128        // threads per block of every persistent kernel
-#define QB_MIN_BLOCKS 6      // resident blocks per SM the traversal kernels are compiled for (80 registers, no spills; 8 measured no faster)
+#ifndef QB_MIN_BLOCKS
+#define QB_MIN_BLOCKS 6      // resident blocks per SM of the closest-hit kernels (80 registers; at 8 = 64 registers they spill and gain nothing)
+#endif
+#ifndef QB_MIN_BLOCKS_ANY
+#define QB_MIN_BLOCKS_ANY 8  // any-hit kernels keep less state: 64 registers without spills, 7 % faster than at 6 (measured)
+#endif
+#ifndef QB_STACK
 #define QB_STACK 48         // deferred far children per ray = max BVH depth supported (the reference keeps 40 entries, objects.cpp:331)
+#endif
 
 struct DNode {
   float4 i0, i1, i2;  // itm column k in xyz, pos[k] in w      (ToNodeCoords)

@@ -103,9 +103,9 @@ __device__ __forceinline__ float plane_t(const Ray3 &r, float z)
 
 // Box::IntersectRay(ray, t_max) for the whole-mesh box (note the non-strict comparisons, unlike the BVH test).
 // exit_out = where the ray leaves the box (QB_BIGFLOAT when every axis is degenerate).
-__device__ __forceinline__ bool mesh_box_hit(const DMesh *__restrict__ m, const Ray3 &r, float t_max, float &exit_out)
+__device__ __forceinline__ bool mesh_box_hit(const DMesh *__restrict__ m, const Ray3 &r, float t_max, float &exit_out, V3 &drcp)
 {
-  const V3 drcp = v3(1.f, 1.f, 1.f) / r.d;
+  drcp = v3(1.f, 1.f, 1.f) / r.d;  // the same quotient TraceBVHNode forms (objects.cpp:333): returned for the traversal
   const V3 bmin = v3(__ldg(&m->bmin[0]), __ldg(&m->bmin[1]), __ldg(&m->bmin[2]));
   const V3 bmax = v3(__ldg(&m->bmax[0]), __ldg(&m->bmax[1]), __ldg(&m->bmax[2]));
   const V3 p0 = -(r.p - bmin) * drcp;
@@ -251,7 +251,8 @@ __device__ __forceinline__ bool object_test(const DScene &S, const DNode *__rest
   const DMesh *m = &S.meshes[__ldg(&n->mesh)];
   if (__ldg(&m->num_faces) == 0u) return false;
   float mexit;
-  if (!mesh_box_hit(m, r, z, mexit)) return false;
+  V3 drcp;
+  if (!mesh_box_hit(m, r, z, mexit, drcp)) return false;
   slot = bvh_trace<ANY>(S, __ldg(&m->root_ref), r, z, uv_slot, uv_t, cnt);
   return slot >= 0;
 }

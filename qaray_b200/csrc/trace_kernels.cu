@@ -168,7 +168,7 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_finish(const DScene S, const Wf
   }
 }
 
-__global__ void __launch_bounds__(QB_BLOCK, QB_MIN_BLOCKS) k_wf_shadow(const DScene S, const WfBuffers B, const WfParams P)
+__global__ void __launch_bounds__(QB_BLOCK, QB_MIN_BLOCKS_ANY) k_wf_shadow(const DScene S, const WfBuffers B, const WfParams P)
 {
   __shared__ uint32_t s_stack[QB_STACK * QB_BLOCK];
   TraceCounters cnt = {0, 0, 0};
@@ -210,7 +210,7 @@ struct WfAreaIO {
   }
 };
 
-__global__ void __launch_bounds__(QB_BLOCK, QB_MIN_BLOCKS) k_wf_area_shadow(const DScene S, const WfBuffers B, const WfParams P)
+__global__ void __launch_bounds__(QB_BLOCK, QB_MIN_BLOCKS_ANY) k_wf_area_shadow(const DScene S, const WfBuffers B, const WfParams P)
 {
   __shared__ uint32_t s_stack[QB_STACK * QB_BLOCK];
   TraceCounters cnt = {0, 0, 0};

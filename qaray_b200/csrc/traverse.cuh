@@ -18,7 +18,9 @@
 namespace qb {
 
 #define QB_REF_EMPTY 0x7FFFFFFFu   // "no current node" (an internal index never reaches 2^31-1)
+#ifndef QB_INNER_REPS
 #define QB_INNER_REPS 3            // node visits per vote while the inner group holds together
+#endif
 
 // what the closest-hit traversal leaves per ray; attributes are computed later by finish_hit (full warps)
 struct HitRec {
@@ -140,14 +142,20 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
               h1 = h1 && !(r.p.z < nc.x - m1 || r.p.z > nc.w + m1);
             }
           }
-          if (h0 && h1) {
+          {
+            // the three outcomes (both children, one, none) as selects + one predicated store / load, so the lanes of the
+            // phase stay converged instead of running three serial branches
+            const bool both = h0 && h1, none = !(h0 || h1);
             const bool first0 = entry0 < entry1;  // the reference pushes the other child first, then this one
-            stk[(sp++) * QB_BLOCK] = first0 ? ndr.y : ndr.x;
-            cur = first0 ? ndr.x : ndr.y;
-          } else if (h0 || h1) {
-            cur = h0 ? ndr.x : ndr.y;
-          } else {
-            cur = sp > 0 ? stk[(--sp) * QB_BLOCK] : QB_REF_EMPTY;
+            const bool take0 = both ? first0 : h0;
+            const uint32_t near_ref = take0 ? ndr.x : ndr.y, far_ref = take0 ? ndr.y : ndr.x;
+            if (both) stk[sp * QB_BLOCK] = far_ref;
+            sp += both ? 1 : 0;
+            const bool pop = none && sp > 0;
+            sp -= pop ? 1 : 0;
+            uint32_t popped = QB_REF_EMPTY;
+            if (pop) popped = stk[sp * QB_BLOCK];
+            cur = none ? popped : near_ref;
           }
         }
       }
@@ -190,9 +198,8 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
           obj_slot = -1; uv_slot = -1;
           if (type == QG_OBJ_MESH) {
             const DMesh *m = &S.meshes[__ldg(&nd->mesh)];
-            if (__ldg(&m->num_faces) != 0u && mesh_box_hit(m, r, h.z, mesh_exit)) {
+            if (__ldg(&m->num_faces) != 0u && mesh_box_hit(m, r, h.z, mesh_exit, drcp)) {
               cur = __ldg(&m->root_ref);
-              drcp = v3(1.f, 1.f, 1.f) / r.d;
               gx = qabs(r.d.x) < 1e-7f; gy = qabs(r.d.y) < 1e-7f; gz = qabs(r.d.z) < 1e-7f;
             }
           } else {
