@@ -64,6 +64,11 @@ struct DevBuf {
     n = count;
     return cudaMalloc((void **) &p, std::max<size_t>(count, 1) * sizeof(T));
   }
+  cudaError_t ensure(size_t count)  // keep the allocation when it is already large enough (no cudaMalloc / cudaFree on the hot path)
+  {
+    if (p && n >= count) return cudaSuccess;
+    return alloc(count);
+  }
   cudaError_t upload(const std::vector<T> &v)
   {
     cudaError_t e = alloc(v.size());
@@ -95,6 +100,9 @@ struct qgScene {
   WfBuffers wf;
   std::vector<void *> wf_allocs;
   uint32_t wf_capacity = 0;
+  // frame-sized device planes of qg_render / qg_resolve, kept between calls
+  DevBuf<float> fr_acc, fr_dep, rs_mean, rs_dep;
+  DevBuf<uint8_t> rs_rgb8, rs_sc, rs_mask;
   int dev_num_area = 0;  // PointLight / SpotLight with size > 0.01 (lights.cpp:52,87)
   DevBuf<unsigned long long> stats;
   cudaStream_t stream = nullptr;
@@ -764,14 +772,15 @@ int resolve_to_host(qgScene *sc, int W, int H, int spp, int srgb, const float *d
                     float *depth, uint8_t *sample_count, uint8_t *mask, cudaStream_t st)
 {
   const size_t n = (size_t) W * H;
-  DevBuf<float> d_mean, d_dep;
-  DevBuf<uint8_t> d_rgb8, d_sc, d_mask;
-  if (rgb_mean) CU(d_mean.alloc(3 * n));
-  if (rgb8) CU(d_rgb8.alloc(3 * n));
-  if (depth) CU(d_dep.alloc(n));
-  if (sample_count) CU(d_sc.alloc(n));
-  if (mask) CU(d_mask.alloc(n));
-  launch_resolve(d_accum, d_depth, (int) n, spp, srgb, d_mean.p, d_rgb8.p, d_dep.p, d_sc.p, d_mask.p, st);
+  DevBuf<float> &d_mean = sc->rs_mean, &d_dep = sc->rs_dep;
+  DevBuf<uint8_t> &d_rgb8 = sc->rs_rgb8, &d_sc = sc->rs_sc, &d_mask = sc->rs_mask;
+  if (rgb_mean) CU(d_mean.ensure(3 * n));
+  if (rgb8) CU(d_rgb8.ensure(3 * n));
+  if (depth) CU(d_dep.ensure(n));
+  if (sample_count) CU(d_sc.ensure(n));
+  if (mask) CU(d_mask.ensure(n));
+  launch_resolve(d_accum, d_depth, (int) n, spp, srgb, rgb_mean ? d_mean.p : nullptr, rgb8 ? d_rgb8.p : nullptr, depth ? d_dep.p : nullptr,
+                 sample_count ? d_sc.p : nullptr, mask ? d_mask.p : nullptr, st);
   if (rgb_mean) CU(cudaMemcpyAsync(rgb_mean, d_mean.p, 3 * n * sizeof(float), cudaMemcpyDeviceToHost, st));
   if (rgb8) CU(cudaMemcpyAsync(rgb8, d_rgb8.p, 3 * n, cudaMemcpyDeviceToHost, st));
   if (depth) CU(cudaMemcpyAsync(depth, d_dep.p, n * sizeof(float), cudaMemcpyDeviceToHost, st));
