@@ -52,6 +52,9 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
   V3 drcp = v3(0.f);
   bool gx = false, gy = false, gz = false;
   float mesh_exit = 0.f;  // where the ray leaves the current mesh's box (bounds the degenerate-axis cull below)
+  float z_entry = 0.f;    // h.z when the current mesh was entered
+  float z_sane = 0.f;     // hits of the current mesh beyond this distance can only be rounding artefacts (see the cull below)
+  int cull_state = 0;     // 0 nothing dropped by the cull yet, 1 something dropped, 2 cull off (exact repeat of the mesh)
   int k = 0, sp = 0;
   uint32_t cur = QB_REF_EMPTY;
   HitRec h;
@@ -119,7 +122,16 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
             // acceptable triangle: an accepted hit point lies inside its triangle's bounds up to rounding, and the ray's
             // coordinate moves by at most |d| * t with t < min(z, exit of the mesh box). Dropping such boxes changes no
             // hit, no distance and no order among the boxes that remain. Margin: twice that travel + 1e-4 relative.
+            // One exception is handled when the mesh is finished (NEXT phase): a triangle almost parallel to the ray gives
+            // t = -pz/dz in the millions, where the barycentric test degenerates to rounding noise and can ACCEPT a point
+            // far outside the triangle (seen: t = 1.9e6 in a 50-unit scene, tests/golden/edge_trc_scene_tower.npz). Such a
+            // hit lies far beyond the mesh box, and it can only surface in the reference's result when nothing nearer was
+            // hit. So if something was dropped and the ray leaves the mesh with z still beyond z_sane = max(box exit,
+            // 1000 box diagonals) — in practice: still without any hit — the mesh is traversed again with the cull off
+            // (cull_state 2), exactly as the reference walks it. A ray that already holds a real hit never pays this.
             const float t_far = qmin(t_max, mesh_exit);
+            const bool h0r = h0, h1r = h1;
+            if (cull_state != 2) {
             if (gx) {
               const float mg = 2.f * qabs(r.d.x) * t_far;
               const float m0 = mg + 1e-4f * qmax(qabs(r.p.x), qmax(qabs(na.x), qabs(na.w)));
@@ -140,6 +152,8 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
               const float m1 = mg + 1e-4f * qmax(qabs(r.p.z), qmax(qabs(nc.x), qabs(nc.w)));
               h0 = h0 && !(r.p.z < na.z - m0 || r.p.z > nb.y + m0);
               h1 = h1 && !(r.p.z < nc.x - m1 || r.p.z > nc.w + m1);
+            }
+            if ((h0r && !h0) || (h1r && !h1)) cull_state = 1;  // something the reference would visit was dropped
             }
           }
           {
@@ -180,7 +194,19 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
       }
     } else if (n_next >= n_fetch) {
       // ---- NEXT: the object just traversed reports its result, then the next object of the list is set up ----------
-      if (s_next) {
+      bool redo = false;
+      if (s_next && k > 0 && cull_state == 1) {
+        // the cull dropped boxes and the mesh produced no hit inside its own box: repeat it exactly as the reference walks it
+        cull_state = 0;
+        if (!(h.z <= z_sane)) {
+          redo = true;
+          cull_state = 2;
+          h.z = z_entry;
+          obj_slot = -1; uv_slot = -1; sp = 0;
+          cur = __ldg(&S.meshes[__ldg(&S.nodes[__ldg(&S.obj_node[k - 1])].mesh)].root_ref);
+        }
+      }
+      if (s_next && !redo) {
         if (k > 0 && obj_slot >= 0) {
           h.k = k - 1; h.slot = obj_slot; h.last_tri = obj_slot;
           if (uv_slot >= 0) { h.tex_k = k - 1; h.tex_slot = uv_slot; h.tex_t = uv_t; }
@@ -200,6 +226,13 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
             const DMesh *m = &S.meshes[__ldg(&nd->mesh)];
             if (__ldg(&m->num_faces) != 0u && mesh_box_hit(m, r, h.z, mesh_exit, drcp)) {
               cur = __ldg(&m->root_ref);
+              cull_state = 0;
+              z_entry = h.z;
+              {
+                const V3 ext = v3(__ldg(&m->bmax[0]) - __ldg(&m->bmin[0]), __ldg(&m->bmax[1]) - __ldg(&m->bmin[1]),
+                                  __ldg(&m->bmax[2]) - __ldg(&m->bmin[2]));
+                z_sane = qmax(mesh_exit * 1.001f, 1000.f * length(ext));
+              }
               gx = qabs(r.d.x) < 1e-7f; gy = qabs(r.d.y) < 1e-7f; gz = qabs(r.d.z) < 1e-7f;
             }
           } else {
