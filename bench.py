@@ -51,6 +51,7 @@ def parse_args():
     ap.add_argument("--width", type=int, default=0)
     ap.add_argument("--height", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--sort-materials", action="store_true", help="qgRenderParams.sort_by_material = 1 (measured option, default off)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target length of the bounded CPU sample")
     return ap.parse_args()
 
@@ -221,7 +222,7 @@ def run_b200_arm(args):
     spp_total = args.spp * world
 
     def params(s0, s1, spp=spp_total):
-        return capi.RenderParams(spp, BOUNCE, 1, 0x5EED, W, H, 0, 1, s0, s1, 0, 0)
+        return capi.RenderParams(spp, BOUNCE, 1, 0x5EED, W, H, 0, 1, s0, s1, 0, 1 if args.sort_materials else 0)
 
     accum = torch.zeros(npix * 4, dtype=torch.float32, device=dev)
     depth = torch.zeros(npix, dtype=torch.float32, device=dev)

@@ -150,7 +150,8 @@ typedef struct qgRenderParams {
   int32_t tile_rank, tile_ranks; /* Renderer::mpiRank / mpiSize: this shard renders 4x4 tiles k = rank (mod ranks) (renderer.cpp:383-387) */
   int32_t sample_begin, sample_end; /* sample-index shard [begin,end); 0,0 = [0,spp) */
   int32_t batch_paths; /* paths in flight per wave; 0 = default */
-  int32_t sort_by_material; /* reserved, must be 0 */
+  int32_t sort_by_material; /* 1 = shade every depth's hits in material order (counting sort of the shade queue); same
+                               image, different warp composition. Default 0: measured slower on the BASELINE scenes */
   int32_t material_class; /* QG_CLASS_*: which MtlBlinn class shades `blinn` materials (the reference picks it with a
                              compile-time alias, src/materials/materials.h:57-61); 0 = MtlBlinn_PhotonMap, its default */
   int32_t spp_min; /* RendererParam::sppMin when below spp (= sppMax): SuperSamplerHalton's adaptive stop

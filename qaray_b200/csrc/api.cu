@@ -432,6 +432,11 @@ int ensure_wf(qgScene *sc, uint32_t capacity, bool carry_diff = false)
     CU(cudaMemset(B.amask, 0, area_cap * 2 * sizeof(uint32_t)));
     B.area_capacity = (uint32_t) area_cap;
   }
+  CU(cudaMalloc((void **) &B.perm, std::max<size_t>(capacity, 1) * sizeof(uint32_t)));
+  sc->wf_allocs.push_back(B.perm);
+  CU(cudaMalloc((void **) &B.mat_bins, 2 * QB_MAT_BINS * sizeof(uint32_t)));
+  sc->wf_allocs.push_back(B.mat_bins);
+  CU(cudaMemset(B.mat_bins, 0, 2 * QB_MAT_BINS * sizeof(uint32_t)));
   CU(cudaMalloc((void **) &B.counters, QB_CNT_WORDS * sizeof(uint32_t)));
   sc->wf_allocs.push_back(B.counters);
   B.stats = sc->stats.p;
@@ -510,6 +515,7 @@ int make_params(const qgScene *sc, const qgRenderParams *rp, WfParams *P, Shard 
   P->seed = rp->seed;
   P->max_bounce = rp->max_bounce;
   P->stale_tex = 1;
+  P->sort_mat = rp->sort_by_material ? 1 : 0;
   if (rp->material_class < QG_CLASS_PHOTONMAP || rp->material_class > QG_CLASS_PHONG_BASIC) return fail(QG_EINVAL, "unknown material_class");
   P->mtl_class = rp->material_class;
   P->carry_diff = class_carries_diff(rp->material_class) ? 1 : 0;
@@ -574,6 +580,10 @@ void run_wave(qgScene *sc, WfParams P, cudaStream_t st, uint64_t *launches, Kern
     P.depth = d;
     launch_wf_trace(sc->dev, B, P, gt, st);
     if (clk) clk->stamp(0);
+    if (P.sort_mat) {
+      launch_mat_sort(sc->dev, B, P, st);
+      *launches += 3;
+    }
     launch_wf_shade(sc->dev, B, P, gs, st);
     if (clk) clk->stamp(1);
     *launches += 2;

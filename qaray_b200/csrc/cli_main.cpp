@@ -42,6 +42,7 @@ int main(int argc, char **argv)
     else if (s == "-device") device = atoi(next());
     else if (s == "-size") { param.width = atoi(next()); param.height = atoi(next()); }
     else if (s == "-shard") { rank = atoi(next()); size = atoi(next()); }
+    else if (s == "-sortmtl") param.sortByMaterial = true;
     else if (s == "-mtl") {  // the reference's compile-time `using MtlBlinn = ...` (materials.h:57-61)
       const std::string c(next());
       if (c == "photonmap") param.materialClass = QG_CLASS_PHOTONMAP;

@@ -29,6 +29,7 @@ struct RendererParam {
   // which class `MtlBlinn` names: a compile-time alias in the reference (src/materials/materials.h:57-61), a run-time
   // switch here (QG_CLASS_*); default = MtlBlinn_PhotonMap like the reference's build
   int materialClass = QG_CLASS_PHOTONMAP;
+  bool sortByMaterial = false;  // shade each depth's hits in material order (qgRenderParams.sort_by_material)
   void SetPhotonMappingFlag(bool f) { usePhotonMap = f; }
   void SetPhotonMapSize(size_t s) { photonMapSize = s; }
   void SetCausticsMapSize(size_t s) { causticsMapSize = s; }
@@ -100,6 +101,7 @@ class Renderer_B200 {
     rp.tile_rank = (int32_t) mpiRank;
     rp.tile_ranks = (int32_t) mpiSize;
     rp.material_class = param.materialClass;
+    rp.sort_by_material = param.sortByMaterial ? 1 : 0;
     rp.spp_min = param.sppMin < param.sppMax ? (int32_t) param.sppMin : 0;  // SuperSamplerHalton's adaptive stop
     if (qg_render(scene, &rp, linearBuffer.data(), colorBuffer.data(), depthBuffer.data(), sampleCountBuffer.data(), maskBuffer.data(),
                   &stats) != QG_OK) {

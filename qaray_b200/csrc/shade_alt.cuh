@@ -95,7 +95,9 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade_alt(const DScene S, const
     if (lane == 0) base = atomicAdd(&B.counters[QB_CNT_FETCH_SHADE + d], 32u);
     base = __shfl_sync(0xFFFFFFFFu, base, 0);
     if (base >= n) break;
-    const uint32_t idx = base + lane;
+    // material-sorted order (qgRenderParams.sort_by_material): queue position -> path index through the permutation
+    // k_mat_scatter built; lanes past the end get n (no work)
+    const uint32_t idx = base + lane < n ? (P.sort_mat ? B.perm[base + lane] : base + lane) : n;
 
     bool shade = false, lights_on = false, front = false;
     V3 p = v3(0.f), N = v3(0.f), V = v3(0.f), T = v3(1.f), Kd = v3(0.f), Ks = v3(0.f);

@@ -14,6 +14,8 @@
 // them (lobe selection, then the lobe's direction sample, then the next hit...), so the same stream fed to the
 // reference gives the same path.
 #include <cstdio>
+#include <cstdlib>
+#include <algorithm>
 #include "wavefront.h"
 #include "trace.cuh"  // Ray3
 
@@ -212,7 +214,9 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade(const DScene S, const WfB
     if (lane == 0) base = atomicAdd(&B.counters[QB_CNT_FETCH_SHADE + d], 32u);
     base = __shfl_sync(0xFFFFFFFFu, base, 0);
     if (base >= n) break;
-    const uint32_t idx = base + lane;
+    // material-sorted order (qgRenderParams.sort_by_material): queue position -> path index through the permutation
+    // k_mat_scatter built; lanes past the end get n (no work)
+    const uint32_t idx = base + lane < n ? (P.sort_mat ? B.perm[base + lane] : base + lane) : n;
 
     bool do_lights = false, alive = false;
     V3 p = v3(0.f), N = v3(0.f), V = v3(0.f), T = v3(1.f), Kd = v3(0.f), Ks = v3(0.f);
@@ -450,6 +454,82 @@ __global__ void k_resolve(const float *__restrict__ accum, const float *__restri
   if (mask) mask[i] = w > 0.f ? 1 : 0;
 }
 
+// ---- material-sorted shading (optional, qgRenderParams.sort_by_material) -----------------------------------------------
+// Counting sort of the depth's shade queue by the material that will shade each hit (MultiMtl resolved), so the lanes of
+// a warp evaluate the same textures / lobes. Three small kernels: histogram, scan, scatter -> B.perm.
+__device__ __forceinline__ uint32_t shade_key(const DScene &S, const WfBuffers &B, uint32_t idx)
+{
+  const float4 h0 = B.h0[idx];
+  const int node = __float_as_int(h0.y);
+  if (node < 0) return 0u;
+  int mi = S.nodes[node].material;
+  if (mi >= 0 && S.materials[mi].kind == QG_MTL_MULTI) {
+    const DMaterial &mm = S.materials[mi];
+    const int mtl_id = __float_as_int(h0.z);
+    mi = (mtl_id >= 0 && mtl_id < mm.sub_count) ? S.multi[mm.sub_first + mtl_id] : -1;
+  }
+  return (uint32_t) min(mi + 2, QB_MAT_BINS - 1);
+}
+__global__ void k_mat_hist(const DScene S, const WfBuffers B, const WfParams P)
+{
+  __shared__ uint32_t s_bins[QB_MAT_BINS];
+  for (int i = threadIdx.x; i < QB_MAT_BINS; i += blockDim.x) s_bins[i] = 0u;
+  __syncthreads();
+  const uint32_t n = P.depth == 0 ? P.n_paths : min(B.counters[QB_CNT_PATHS + P.depth], B.capacity);
+  for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += gridDim.x * blockDim.x) atomicAdd(&s_bins[shade_key(S, B, idx)], 1u);
+  __syncthreads();
+  for (int i = threadIdx.x; i < QB_MAT_BINS; i += blockDim.x)
+    if (s_bins[i]) atomicAdd(&B.mat_bins[i], s_bins[i]);
+}
+__global__ void k_mat_scan(const WfBuffers B)
+{
+  if (threadIdx.x != 0) return;
+  uint32_t run = 0u;
+  for (int i = 0; i < QB_MAT_BINS; ++i) {
+    B.mat_bins[QB_MAT_BINS + i] = run;
+    run += B.mat_bins[i];
+    B.mat_bins[i] = 0u;  // clean for the next depth
+  }
+}
+// Tile-local counting scatter: a block ranks a tile of QB_SORT_TILE hits per material in shared memory, reserves one range
+// per non-empty bin with ONE global atomic, and writes its indices there — the global atomics drop from one per hit to
+// one per (tile, material), and a material's run in B.perm is made of chunks whose indices come from one 1024-hit window
+// of the queue, so the gathered path-state reads of shade stay sector-local.
+#define QB_SORT_ITEMS 4
+#define QB_SORT_TILE (256 * QB_SORT_ITEMS)
+__global__ void __launch_bounds__(256) k_mat_scatter(const DScene S, const WfBuffers B, const WfParams P)
+{
+  __shared__ uint32_t s_cnt[QB_MAT_BINS], s_base[QB_MAT_BINS];
+  const uint32_t n = P.depth == 0 ? P.n_paths : min(B.counters[QB_CNT_PATHS + P.depth], B.capacity);
+  for (uint32_t tile = blockIdx.x * QB_SORT_TILE; tile < n; tile += gridDim.x * QB_SORT_TILE) {
+    s_cnt[threadIdx.x] = 0u;  // blockDim.x == QB_MAT_BINS == 256
+    __syncthreads();
+    uint32_t key[QB_SORT_ITEMS], rank[QB_SORT_ITEMS];
+#pragma unroll
+    for (int i = 0; i < QB_SORT_ITEMS; ++i) {
+      const uint32_t idx = tile + i * 256 + threadIdx.x;
+      key[i] = idx < n ? shade_key(S, B, idx) : 0u;
+      rank[i] = idx < n ? atomicAdd(&s_cnt[key[i]], 1u) : 0u;
+    }
+    __syncthreads();
+    if (s_cnt[threadIdx.x]) s_base[threadIdx.x] = atomicAdd(&B.mat_bins[QB_MAT_BINS + threadIdx.x], s_cnt[threadIdx.x]);
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < QB_SORT_ITEMS; ++i) {
+      const uint32_t idx = tile + i * 256 + threadIdx.x;
+      if (idx < n) B.perm[s_base[key[i]] + rank[i]] = idx;
+    }
+    __syncthreads();
+  }
+}
+void launch_mat_sort(const DScene &S, const WfBuffers &B, const WfParams &P, cudaStream_t st)
+{
+  k_mat_hist<<<148 * 4, 256, 0, st>>>(S, B, P);
+  k_mat_scan<<<1, 32, 0, st>>>(B);
+  static_assert(QB_MAT_BINS == 256, "k_mat_scatter uses one thread per bin");
+  k_mat_scatter<<<148 * 8, 256, 0, st>>>(S, B, P);
+}
+
 // ---- adaptive sampling: SuperSamplerHalton (src/scene/scene.cpp:83-123) -----------------------------------------------------
 // The reference loops per pixel: sample, Accumulate (running mean + a variance proxy), stop when s >= sppMin and every
 // channel's proxy is below (0.005, 0.001, 0.005), or at sppMax. Sample s of a pixel is a pure function of (pixel, s, seed)
@@ -547,27 +627,29 @@ __global__ void k_wf_stats(const uint32_t *__restrict__ counters, unsigned long 
 }
 void launch_wf_stats(const WfBuffers &B, int max_bounce, cudaStream_t st) { k_wf_stats<<<1, 1, 0, st>>>(B.counters, B.stats, max_bounce); }
 
-static int persistent_grid_shade()
+// persistent grid of one shade kernel: every SM filled to that kernel's own residency (the classes differ a lot in
+// registers, so one grid for all would hold the default class at the heaviest class's 3 blocks / SM)
+static int persistent_grid_shade(const void *kernel)
 {
   int dev = 0, sms = 0, per_sm = 0;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, (const void *) k_wf_shade, QB_BLOCK, 0);
-  int alt = 0;  // one grid size for every class: the smallest residency (a persistent grid must be fully resident)
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&alt, (const void *) k_wf_shade_alt<QG_CLASS_MONTECARLOGI, false>, QB_BLOCK, 0);
-  if (alt >= 1 && alt < per_sm) per_sm = alt;
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&alt, (const void *) k_wf_shade_alt<QG_CLASS_BLINN_BASIC, false>, QB_BLOCK, 0);
-  if (alt >= 1 && alt < per_sm) per_sm = alt;
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&alt, (const void *) k_wf_shade_alt<QG_CLASS_PATHTRACING, false>, QB_BLOCK, 0);
-  if (alt >= 1 && alt < per_sm) per_sm = alt;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, QB_BLOCK, 0);
   if (per_sm < 1) per_sm = 1;
+  if (per_sm > 4) per_sm = 4;  // measured: 4 blocks / SM is the knee (xmas shade 104.7 / 92.9 / 93.5 ms at 3 / 4 / 5, tower 11.3 / 10.8 / 13.1)
+  if (const char *e = getenv("QB_SHADE_BLOCKS")) per_sm = std::max(1, std::min(per_sm, atoi(e)));  // A/B override
   return sms * per_sm;
 }
-int wf_shade_grid() { static int g = persistent_grid_shade(); return g; }
+int wf_shade_grid() { static int g = persistent_grid_shade((const void *) k_wf_shade); return g; }
+template <int C, bool PRIMARY> static int alt_grid()
+{
+  static int g = persistent_grid_shade((const void *) k_wf_shade_alt<C, PRIMARY>);
+  return g;
+}
 
 void launch_wf_shade(const DScene &S, const WfBuffers &B, const WfParams &P, int grid, cudaStream_t st)
 {
-#define ALT(C) (P.depth == 0 ? k_wf_shade_alt<C, true><<<grid, QB_BLOCK, 0, st>>>(S, B, P) : k_wf_shade_alt<C, false><<<grid, QB_BLOCK, 0, st>>>(S, B, P))
+#define ALT(C) (P.depth == 0 ? k_wf_shade_alt<C, true><<<alt_grid<C, true>(), QB_BLOCK, 0, st>>>(S, B, P) : k_wf_shade_alt<C, false><<<alt_grid<C, false>(), QB_BLOCK, 0, st>>>(S, B, P))
   switch (P.mtl_class) {
     case QG_CLASS_PATHTRACING: ALT(QG_CLASS_PATHTRACING); break;
     case QG_CLASS_MONTECARLOGI: ALT(QG_CLASS_MONTECARLOGI); break;

@@ -35,6 +35,7 @@ namespace qb {
 #define QB_CNT_WORDS 112
 
 // area lights (PointLight / SpotLight with size > 0.01, src/lights/lights.cpp:50-65,84-101): shadow samples per group
+#define QB_MAT_BINS 256        // material sort: bin 0 = miss, 1 = no material / MultiMtl out of range, 2 + i = material i
 #define QB_AREA_SPP_MIN 16     // GenLight::shadow_spp_min (lights.cpp:16)
 #define QB_AREA_SPP_MAX 64     // GenLight::shadow_spp_max (lights.cpp:17)
 
@@ -65,6 +66,9 @@ struct WfBuffers {
   float4 *a2;       // contribution.rgb per unit of the light's visibility estimate
   uint32_t *amask;  // 2 words per group: bit s = shadow sample s reached the light
   uint32_t area_capacity;
+  // material sort of the shade queue (optional): permutation and the per-material bins / offsets
+  uint32_t *perm;      // capacity entries
+  uint32_t *mat_bins;  // 2 * QB_MAT_BINS: counts, then running offsets
   uint32_t *counters;
   unsigned long long *stats;  // [0] closest rays, [1] shadow rays, [2] nodes, [3] tris, [4] objects
   uint32_t capacity;          // paths per wave
@@ -89,6 +93,7 @@ struct WfParams {
   int32_t max_bounce;
   int32_t depth;             // current depth d
   int32_t stale_tex;
+  int32_t sort_mat;          // 1: shade(d) walks its queue in material order (B.perm)
   int32_t mtl_class;         // QG_CLASS_*: which of the reference's MtlBlinn classes shades (materials.h:57-61)
   int32_t carry_diff;        // secondary paths carry differential rays (ps4..ps6 / h4 allocated)
   int32_t no_falloff;        // DisableInverseSquareFalloff() was called (MtlBlinn_Basic.cpp:18, lights.cpp:21-30)
@@ -156,6 +161,7 @@ void launch_wf_trace(const DScene &S, const WfBuffers &B, const WfParams &P, int
 void launch_wf_shadow(const DScene &S, const WfBuffers &B, const WfParams &P, int grid, cudaStream_t st);
 void launch_wf_shade(const DScene &S, const WfBuffers &B, const WfParams &P, int grid, cudaStream_t st);
 void launch_wf_area(const DScene &S, const WfBuffers &B, const WfParams &P, int grid, cudaStream_t st);  // area shadow rays + resolve
+void launch_mat_sort(const DScene &S, const WfBuffers &B, const WfParams &P, cudaStream_t st);  // builds B.perm for shade(P.depth)
 void launch_wf_stats(const WfBuffers &B, int max_bounce, cudaStream_t st);
 // adaptive sampling (SuperSamplerHalton, src/scene/scene.cpp:83-123), see shade_kernels.cu
 void launch_adaptive_build(int W, int H, int tile_rank, int tile_ranks, const int32_t *count, const uint8_t *active, int chunk,
