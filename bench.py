@@ -323,10 +323,11 @@ def finish_b200(args, L):
                "s_objects": sc.shadow_objects_tested}
         t = dev_run["tot"]  # rank 0's own totals over the timed steps
         bytes_c, bytes_s, per_c, per_s = algorithmic_bytes(t["closest"], t["shadow"], cst)
-        if t["trace_ms"] >= t["shadow_ms"]:
-            kname, kbytes, kms, klaunch = "k_wf_trace (closest-hit traversal)", bytes_c, t["trace_ms"], per_c
-        else:
-            kname, kbytes, kms, klaunch = "k_wf_shadow (any-hit traversal)", bytes_s, t["shadow_ms"], per_s
+        # The dominant kernel is the traversal core traverse_pool<ANY> in its two instantiations: k_wf_trace (closest hit) and
+        # k_wf_shadow (any hit). shadow(d) runs beside trace(d + 1) on a second stream, so the two are timed as one: trace_ms +
+        # shadow_ms is the CUDA-event time during which a traversal kernel was running (qgRenderStats), bytes are both kernels'.
+        kname, kbytes, kms = "traverse_pool: k_wf_trace + k_wf_shadow (concurrent streams)", bytes_c + bytes_s, t["trace_ms"] + t["shadow_ms"]
+        klaunch = kbytes / max(1.0, float(t["closest"] + t["shadow"]))
         peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
         if os.path.exists(peaks_path):
             peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
@@ -338,12 +339,11 @@ def finish_b200(args, L):
         achieved = kbytes / (kms * 1e-3) * 1e-9 if kms > 0 else 0.0
         traffic = None
         tp = os.path.join(ROOT, "profiles", "traffic.json")  # DRAM bytes per ray of the kernel from the ncu --set full capture
-        klaunches = max(1, (BOUNCE + 1) * args.steps * n_waves)
+        klaunches = max(1, (BOUNCE + 1) * args.steps * n_waves * (2 if t["shadow"] > 0 else 1))
         if os.path.exists(tp):
-            rec = json.load(open(tp)).get(kname.split(" ")[0])
-            if rec:
-                krays = t["closest"] if kname.startswith("k_wf_trace") else t["shadow"]
-                traffic = rec["dram_bytes_per_ray"] * krays / klaunches  # per launch, like achieved's bytes
+            rec = json.load(open(tp))
+            if "k_wf_trace" in rec and "k_wf_shadow" in rec:  # per launch, like achieved's bytes
+                traffic = (rec["k_wf_trace"]["dram_bytes_per_ray"] * t["closest"] + rec["k_wf_shadow"]["dram_bytes_per_ray"] * t["shadow"]) / klaunches
         roofline = {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                     "traffic": traffic, "peak_source": peak_src, "bytes_per_ray": klaunch, "kernel_ms_per_step": kms / args.steps,
                     "launches_of_kernel": klaunches, "algorithmic_bytes_per_launch": kbytes / klaunches,

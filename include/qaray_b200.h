@@ -166,7 +166,10 @@ typedef struct qgRenderStats {
   uint64_t nodes_visited, tris_tested, objects_tested; /* closest-hit rays; filled by the counting build only, else 0 */
   uint64_t shadow_nodes_visited, shadow_tris_tested, shadow_objects_tested; /* same for any-hit rays */
   double device_ms;       /* CUDA-event time of the render on its stream */
-  double trace_ms, shade_ms, shadow_ms; /* summed launch durations per kernel class (closest-hit, shade, any-hit) */
+  double trace_ms, shade_ms, shadow_ms; /* device time per kernel class: closest-hit (+ hit attributes), shade, and the any-hit
+                                           time not already inside a closest-hit interval (the any-hit kernels of depth d run
+                                           beside the closest-hit kernel of depth d + 1): trace_ms + shadow_ms = time some
+                                           traversal kernel was running */
 } qgRenderStats;
 
 typedef struct qgSceneInfo {

@@ -9,6 +9,8 @@
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <cstdlib>
+#include <utility>
 #include <vector>
 
 #include "../../include/qaray_b200.h"
@@ -107,9 +109,14 @@ struct qgScene {
   DevBuf<unsigned long long> stats;
   cudaStream_t stream = nullptr;
   std::vector<cudaEvent_t> ev_pool;  // timestamp events of KernelClock
+  cudaStream_t shadow_stream = nullptr;  // shadow(d) runs here, beside trace(d + 1) (run_wave)
+  cudaEvent_t ev_shade = nullptr, ev_shadow = nullptr;
   ~qgScene()
   {
     for (cudaEvent_t e : ev_pool) cudaEventDestroy(e);
+    if (ev_shade) cudaEventDestroy(ev_shade);
+    if (ev_shadow) cudaEventDestroy(ev_shadow);
+    if (shadow_stream) cudaStreamDestroy(shadow_stream);
     for (void *p : wf_allocs) cudaFree(p);
     if (stream) cudaStreamDestroy(stream);
   }
@@ -378,6 +385,9 @@ int upload_scene(qgScene *sc)
   }
   upload_texture_taps(taps);
   CU(cudaStreamCreateWithFlags(&sc->stream, cudaStreamNonBlocking));
+  CU(cudaStreamCreateWithFlags(&sc->shadow_stream, cudaStreamNonBlocking));
+  CU(cudaEventCreateWithFlags(&sc->ev_shade, cudaEventDisableTiming));
+  CU(cudaEventCreateWithFlags(&sc->ev_shadow, cudaEventDisableTiming));
   CU(cudaDeviceSynchronize());
   return QG_OK;
 }
@@ -547,8 +557,10 @@ struct KernelClock {
   cudaStream_t st;
   bool on;
   size_t used = 0;
-  std::vector<int> cls;
-  void stamp(int c)
+  std::vector<int> cls;   // class of the interval that ENDS at this event; -1 = the event only opens an interval
+  std::vector<int> prev;  // the event that opens it: the previous one recorded on the same stream
+  int last_main = -1, last_side = -1;
+  void stamp(int c, cudaStream_t s = nullptr)
   {
     if (!on) return;
     if (used == sc->ev_pool.size()) {
@@ -556,50 +568,105 @@ struct KernelClock {
       if (cudaEventCreate(&e) != cudaSuccess) { on = false; return; }
       sc->ev_pool.push_back(e);
     }
-    cudaEventRecord(sc->ev_pool[used++], st);
+    const bool side = s != nullptr && s == sc->shadow_stream;
+    cudaEventRecord(sc->ev_pool[used], s ? s : st);
+    int &last = side ? last_side : last_main;
     cls.push_back(c);
+    prev.push_back(last);
+    last = (int) used++;
   }
+  // out[0] trace + finish, out[1] shade, out[2] any-hit time NOT already covered by a trace interval (the any-hit kernels
+  // run beside trace(d + 1) on a second stream), out[3] other: out[0] + out[2] is the time some traversal kernel was running
   void sums(double out[4]) const
   {
     for (int k = 0; k < 4; ++k) out[k] = 0.0;
-    for (size_t i = 1; i < used; ++i) {
-      float ms = 0.f;
-      if (cudaEventElapsedTime(&ms, sc->ev_pool[i - 1], sc->ev_pool[i]) == cudaSuccess) out[cls[i]] += ms;
+    std::vector<std::pair<float, float>> tr, sh;
+    for (size_t i = 0; i < used; ++i) {
+      float t0 = 0.f, t1 = 0.f;
+      if (cls[i] < 0 || prev[i] < 0) continue;
+      if (cudaEventElapsedTime(&t0, sc->ev_pool[0], sc->ev_pool[prev[i]]) != cudaSuccess) continue;
+      if (cudaEventElapsedTime(&t1, sc->ev_pool[0], sc->ev_pool[i]) != cudaSuccess) continue;
+      if (cls[i] == 0) tr.push_back({t0, t1});
+      if (cls[i] == 2) sh.push_back({t0, t1});
+      else out[cls[i]] += (double) (t1 - t0);
+    }
+    std::sort(sh.begin(), sh.end());
+    float covered_to = -1.f;
+    for (auto iv : sh) {  // any-hit intervals are serial on their stream; subtract what the trace intervals cover
+      float lo = std::max(iv.first, covered_to), hi = iv.second;
+      if (hi <= lo) continue;
+      double len = (double) (hi - lo);
+      for (auto t : tr) {
+        const float a = std::max(lo, t.first), b = std::min(hi, t.second);
+        if (b > a) len -= (double) (b - a);
+      }
+      out[2] += std::max(0.0, len);
+      covered_to = hi;
     }
   }
 };
 
-// one wave: depth loop of trace -> shade -> shadow, all on `st`, no host synchronisation
+// One wave: the depth loop trace -> finish -> shade -> shadow with no host synchronisation. The shadow rays of depth d
+// only add into the frame, so they run on a second stream beside trace(d + 1) / finish(d + 1): every traversal launch
+// ends in a latency-bound tail (its longest rays), and the other kernel's blocks fill the SMs that tail leaves idle.
+// trace(d + 1) is launched first so that it owns the SMs and shadow(d) fills in; shade(d + 1) rewrites the shadow queue
+// and therefore waits for shadow(d). (Running the main chain on a higher-priority stream changed nothing: measured.)
 void run_wave(qgScene *sc, WfParams P, cudaStream_t st, uint64_t *launches, KernelClock *clk = nullptr)
 {
   const WfBuffers &B = sc->wf;
+  static const bool serial = getenv("QB_SERIAL_SHADOW") != nullptr;  // A/B: everything on one stream
+  cudaStream_t st2 = serial ? st : sc->shadow_stream;
   cudaMemsetAsync(B.counters, 0, QB_CNT_WORDS * sizeof(uint32_t), st);
-  if (clk) clk->stamp(3);
+  if (clk) clk->stamp(3, st);
   const int gt = wf_trace_grid(), gs = wf_shade_grid(), gsh = wf_shadow_grid();
-  for (int d = 0; d <= P.max_bounce; ++d) {
+  const bool any_shadow = sc->dev.num_nonambient > 0 || sc->dev_num_area > 0;
+  auto shade = [&](int d) {
     P.depth = d;
-    launch_wf_trace(sc->dev, B, P, gt, st);
-    if (clk) clk->stamp(0);
     if (P.sort_mat) {
       launch_mat_sort(sc->dev, B, P, st);
       *launches += 3;
     }
     launch_wf_shade(sc->dev, B, P, gs, st);
-    if (clk) clk->stamp(1);
-    *launches += 2;
-    if (sc->dev.num_nonambient > 0) {
-      launch_wf_shadow(sc->dev, B, P, gsh, st);
-      if (clk) clk->stamp(2);
-      *launches += 1;
+    if (clk) clk->stamp(1, st);
+    *launches += 1;
+    if (any_shadow && st2 != st) cudaEventRecord(sc->ev_shade, st);
+  };
+  auto trace = [&](int d) {
+    P.depth = d;
+    launch_wf_trace(sc->dev, B, P, gt, st);
+    if (clk) clk->stamp(0, st);
+    *launches += 2;  // traversal + hit attributes
+  };
+  trace(0);
+  shade(0);
+  for (int d = 0; d <= P.max_bounce; ++d) {
+    if (d < P.max_bounce) trace(d + 1);
+    if (any_shadow) {
+      P.depth = d;
+      if (st2 != st) {
+        cudaStreamWaitEvent(st2, sc->ev_shade, 0);
+        if (clk) clk->stamp(-1, st2);
+      }
+      if (sc->dev.num_nonambient > 0) {
+        launch_wf_shadow(sc->dev, B, P, gsh, st2);
+        if (clk) clk->stamp(2, st2);
+        *launches += 1;
+      }
+      if (sc->dev_num_area > 0) {
+        launch_wf_area(sc->dev, B, P, gsh, st2);
+        if (clk) clk->stamp(2, st2);
+        *launches += 2;
+      }
+      if (st2 != st) {
+        cudaEventRecord(sc->ev_shadow, st2);
+        cudaStreamWaitEvent(st, sc->ev_shadow, 0);  // before shade(d + 1), or the end of the wave
+        if (clk) clk->stamp(-1, st);
+      }
     }
-    if (sc->dev_num_area > 0) {
-      launch_wf_area(sc->dev, B, P, gsh, st);
-      if (clk) clk->stamp(2);
-      *launches += 2;
-    }
+    if (d < P.max_bounce) shade(d + 1);
   }
   launch_wf_stats(B, P.max_bounce, st);
-  if (clk) clk->stamp(3);
+  if (clk) clk->stamp(3, st);
   *launches += 1;
 }
 
