@@ -1,5 +1,5 @@
 run() { python bench.py --no-cpu-baseline --steps 5 --warmup 3 "$@" > /tmp/o.json 2>/tmp/o.err
-python - "NOPRIO=$QB_NO_PRIORITY $*" <<'PY' >> gpurun_out/ab.txt
+python - "SORT_RAYS=$QB_SORT_RAYS $*" <<'PY' >> gpurun_out/ab.txt
 import json,sys
 try:
     d=json.loads(open('/tmp/o.json').read().strip().splitlines()[-1]); r=d['roofline']['class_ms_per_step']
@@ -8,11 +8,8 @@ except Exception as e:
     print(sys.argv[1], 'FAILED', open('/tmp/o.err').read()[-300:])
 PY
 }
-run --scene trc_scene_tower
-run --scene trc_scene_xmas
-export QB_NO_PRIORITY=1
-run --scene trc_scene_tower
-run --scene trc_scene_xmas
-unset QB_NO_PRIORITY
+for m in 0 1 2 3; do export QB_SORT_RAYS=$m; run --scene trc_scene_tower; done
+export QB_SORT_RAYS=3
 python -m pytest tests -x -q -m gpu 2>&1 | tail -3 >> gpurun_out/ab.txt
+run --scene trc_scene_xmas
 cat gpurun_out/ab.txt
