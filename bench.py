@@ -333,8 +333,8 @@ def finish_b200(args, L):
             peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
         else:
             peak, peak_src = 6650.0, "B200_PROFILING.md fallback (of fallback)"
-        # launches per wave = 1 (stats) + (bounce + 1) x (trace + finish + shade [+ shadow]); waves per step follow
-        per_wave = 1 + (BOUNCE + 1) * (3 + (1 if t["shadow"] > 0 else 0))
+        # launches per wave = 1 (stats) + (bounce + 1) x (trace + 2 cull-check kernels + finish + shade [+ shadow]); waves per step follow
+        per_wave = 1 + (BOUNCE + 1) * (5 + (1 if t["shadow"] > 0 else 0))
         n_waves = max(1, int(round(t["launches"] / float(args.steps) / per_wave)))
         achieved = kbytes / (kms * 1e-3) * 1e-9 if kms > 0 else 0.0
         traffic = None

@@ -442,6 +442,9 @@ int ensure_wf(qgScene *sc, uint32_t capacity, bool carry_diff = false)
     CU(cudaMemset(B.amask, 0, area_cap * 2 * sizeof(uint32_t)));
     B.area_capacity = (uint32_t) area_cap;
   }
+  B.redo_capacity = 1u << 18;
+  CU(cudaMalloc((void **) &B.redo, (size_t) B.redo_capacity * sizeof(uint4)));
+  sc->wf_allocs.push_back(B.redo);
   CU(cudaMalloc((void **) &B.perm, std::max<size_t>(capacity, 1) * sizeof(uint32_t)));
   sc->wf_allocs.push_back(B.perm);
   CU(cudaMalloc((void **) &B.mat_bins, 2 * QB_MAT_BINS * sizeof(uint32_t)));
@@ -635,7 +638,7 @@ void run_wave(qgScene *sc, WfParams P, cudaStream_t st, uint64_t *launches, Kern
     P.depth = d;
     launch_wf_trace(sc->dev, B, P, gt, st);
     if (clk) clk->stamp(0, st);
-    *launches += 2;  // traversal + hit attributes
+    *launches += 4;  // traversal, the two cull-check kernels, hit attributes
   };
   trace(0);
   shade(0);

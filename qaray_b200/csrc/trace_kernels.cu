@@ -57,6 +57,20 @@ __device__ __forceinline__ HitRec get_rec(const float4 *r0, const float4 *r1, ui
   return h;
 }
 
+struct RedoQueue {
+  uint4 *q;          // {ray index, object, z at mesh entry (bits), flag}
+  uint32_t cap;
+  uint32_t *count;   // entries pushed (may run past cap: clamp)
+  uint32_t *fetch;   // work cursor of the exact pass
+};
+__device__ __forceinline__ bool redo_push(const RedoQueue &Q, uint32_t idx, int k, float z_entry)
+{
+  if (Q.cap == 0u) return false;
+  const uint32_t q = atomicAdd(Q.count, 1u);
+  if (q >= Q.cap) return false;
+  Q.q[q] = make_uint4(idx, (uint32_t) k, __float_as_uint(z_entry), 0u);
+  return true;
+}
 template <bool PRIMARY>
 struct WfClosestIO {
   const WfBuffers &B;
@@ -64,6 +78,13 @@ struct WfClosestIO {
   uint32_t n;
   __device__ uint32_t count() const { return n; }
   __device__ uint32_t *cursor() { return &B.counters[QB_CNT_FETCH_TRACE + P.depth]; }
+  __device__ uint32_t map(uint32_t q) const { return q; }
+  __device__ bool exact() const { return false; }
+  // hand a (ray, mesh) whose culled walk dropped boxes and found nothing to the redo kernels; false when the queue is full
+  __device__ bool defer(uint32_t idx, int k, float z_entry) const
+  {
+    return redo_push(RedoQueue{B.redo, B.redo_capacity, &B.counters[QB_CNT_REDO + P.depth], nullptr}, idx, k, z_entry);
+  }
   __device__ bool load(uint32_t idx, Ray3 &c, float &tmax)
   {
     tmax = QB_BIGFLOAT;
@@ -92,6 +113,9 @@ struct WfShadowIO {
   uint32_t n;
   __device__ uint32_t count() const { return n; }
   __device__ uint32_t *cursor() { return &B.counters[QB_CNT_FETCH_SHADOW + P.depth]; }
+  __device__ uint32_t map(uint32_t q) const { return q; }                 // queue position -> ray index
+  __device__ bool exact() const { return false; }                          // true: degenerate-axis cull off for every mesh
+  __device__ bool defer(uint32_t, int, float) const { return false; }      // false: the lane repeats the mesh itself
   __device__ bool load(uint32_t idx, Ray3 &c, float &tmax)
   {
     const float4 a = B.s0[idx], b = B.s1[idx];
@@ -119,6 +143,76 @@ __global__ void __launch_bounds__(QB_BLOCK, QB_MIN_BLOCKS) k_wf_trace(const DSce
   __shared__ uint32_t s_stack[QB_STACK * QB_BLOCK];
   TraceCounters cnt = {0, 0, 0};
   WfClosestIO<PRIMARY> io{B, P, PRIMARY ? P.n_paths : min(B.counters[QB_CNT_PATHS + P.depth], B.capacity)};
+  traverse_pool<false>(S, io, s_stack, cnt);
+  flush_counters(B.stats, cnt);
+}
+
+// ---- deferred check of the degenerate-axis cull ----------------------------------------------------------------------------
+// trace(d) queued the (ray, mesh) pairs whose culled walk dropped boxes and found nothing (traverse.cuh). The reference walks
+// every box such a ray's two regular axes cross and can accept a rounding-noise hit there (t ~ 1e6 on a triangle the ray
+// never touches). k_redo_detect decides with the whole GPU whether ANY triangle of the mesh accepts the ray — a superset of
+// what the reference tests, so "none" proves the stored record exact (the usual outcome). A pair with an accepting triangle
+// is re-traced by k_redo_exact with the cull off from the first object on, i.e. exactly as the reference walks it, and its
+// record is overwritten.
+template <class IO> __device__ __forceinline__ void redo_detect(const DScene &S, IO &io, const RedoQueue &Q)
+{
+  const uint32_t n = min(*Q.count, Q.cap);
+  const DNode *root = &S.nodes[0];
+  for (uint32_t e = 0; e < n; ++e) {
+    const uint4 ent = Q.q[e];
+    Ray3 c;
+    float tmax;
+    if (!io.load(ent.x, c, tmax)) continue;
+    const int k = (int) ent.y;
+    const Ray3 r = chain_ray(S, k, to_node(root, c));
+    const DMesh *m = &S.meshes[__ldg(&S.nodes[__ldg(&S.obj_node[k])].mesh)];
+    const uint32_t first = __ldg(&m->face_base), count = __ldg(&m->num_faces);  // triangle slots of a mesh = its face range
+    const float z_entry = __uint_as_float(ent.z);
+    bool any = false;
+    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < count; t += gridDim.x * blockDim.x) {
+      const DTri *tp = &S.tris[first + t];
+      const float4 ta = __ldg(&tp->a), tb = __ldg(&tp->b), tc = __ldg(&tp->c), td = __ldg(&tp->d);
+      float tt;
+      any = any || tri_accept(r, z_entry, xyz(ta), xyz(tb), xyz(tc), v3(ta.w, tb.w, tc.w), td.x, __float_as_int(td.y), tt);
+    }
+    if (any) Q.q[e].w = 1u;
+  }
+}
+// the flagged pairs' rays through the same traversal core with the cull off; records overwritten through the base IO
+template <class IO>
+struct RedoIO {
+  IO &base;
+  RedoQueue Q;
+  uint32_t n;
+  __device__ uint32_t count() const { return n; }
+  __device__ uint32_t *cursor() { return Q.fetch; }
+  __device__ uint32_t map(uint32_t q) const { return Q.q[q].w ? Q.q[q].x : 0xFFFFFFFFu; }
+  __device__ bool exact() const { return true; }
+  __device__ bool defer(uint32_t, int, float) const { return false; }
+  __device__ bool load(uint32_t idx, Ray3 &c, float &tmax) { return idx != 0xFFFFFFFFu && base.load(idx, c, tmax); }
+  __device__ void store(uint32_t idx, const HitRec &h) { base.store(idx, h); }
+  __device__ void store_any(uint32_t, bool) {}
+};
+__device__ __forceinline__ RedoQueue wf_redo_queue(const WfBuffers &B, const WfParams &P)
+{
+  return RedoQueue{B.redo, B.redo_capacity, &B.counters[QB_CNT_REDO + P.depth], &B.counters[QB_CNT_FETCH_REDO + P.depth]};
+}
+template <bool PRIMARY>
+__global__ void __launch_bounds__(QB_BLOCK) k_redo_detect(const DScene S, const WfBuffers B, const WfParams P)
+{
+  if (B.counters[QB_CNT_REDO + P.depth] == 0u) return;
+  WfClosestIO<PRIMARY> io{B, P, 0u};
+  redo_detect(S, io, wf_redo_queue(B, P));
+}
+template <bool PRIMARY>
+__global__ void __launch_bounds__(QB_BLOCK, QB_MIN_BLOCKS) k_redo_exact(const DScene S, const WfBuffers B, const WfParams P)
+{
+  __shared__ uint32_t s_stack[QB_STACK * QB_BLOCK];
+  const uint32_t n = min(B.counters[QB_CNT_REDO + P.depth], B.redo_capacity);
+  if (n == 0u) return;
+  TraceCounters cnt = {0, 0, 0};
+  WfClosestIO<PRIMARY> base{B, P, 0u};
+  RedoIO<WfClosestIO<PRIMARY>> io{base, wf_redo_queue(B, P), n};
   traverse_pool<false>(S, io, s_stack, cnt);
   flush_counters(B.stats, cnt);
 }
@@ -189,6 +283,9 @@ struct WfAreaIO {
   uint32_t n;  // QB_AREA_SPP_MAX * groups
   __device__ uint32_t count() const { return n; }
   __device__ uint32_t *cursor() { return &B.counters[QB_CNT_FETCH_AREA + P.depth]; }
+  __device__ uint32_t map(uint32_t q) const { return q; }                 // queue position -> ray index
+  __device__ bool exact() const { return false; }                          // true: degenerate-axis cull off for every mesh
+  __device__ bool defer(uint32_t, int, float) const { return false; }      // false: the lane repeats the mesh itself
   __device__ bool load(uint32_t idx, Ray3 &c, float &tmax)
   {
     const uint32_t g = idx / QB_AREA_SPP_MAX;
@@ -270,8 +367,12 @@ struct RayBufClosestIO {
   uint32_t n;
   uint32_t *cur;
   float4 *r0, *r1;
+  RedoQueue Q;
   __device__ uint32_t count() const { return n; }
   __device__ uint32_t *cursor() { return cur; }
+  __device__ uint32_t map(uint32_t q) const { return q; }
+  __device__ bool exact() const { return false; }
+  __device__ bool defer(uint32_t idx, int k, float z_entry) const { return redo_push(Q, idx, k, z_entry); }
   __device__ bool load(uint32_t idx, Ray3 &c, float &tmax)
   {
     tmax = QB_BIGFLOAT;
@@ -290,6 +391,9 @@ struct RayBufAnyIO {
   uint8_t *occ;
   __device__ uint32_t count() const { return n; }
   __device__ uint32_t *cursor() { return cur; }
+  __device__ uint32_t map(uint32_t q) const { return q; }                 // queue position -> ray index
+  __device__ bool exact() const { return false; }                          // true: degenerate-axis cull off for every mesh
+  __device__ bool defer(uint32_t, int, float) const { return false; }      // false: the lane repeats the mesh itself
   __device__ bool load(uint32_t idx, Ray3 &c, float &tmax)
   {
     c.p = v3(rays6[6 * idx + 0], rays6[6 * idx + 1], rays6[6 * idx + 2]);
@@ -387,9 +491,13 @@ void launch_wf_trace(const DScene &S, const WfBuffers &B, const WfParams &P, int
   const int fg = 148 * 8;
   if (P.depth == 0) {
     k_wf_trace<true><<<grid, QB_BLOCK, 0, st>>>(S, B, P);
+    k_redo_detect<true><<<148 * 8, QB_BLOCK, 0, st>>>(S, B, P);
+    k_redo_exact<true><<<148, QB_BLOCK, 0, st>>>(S, B, P);
     k_wf_finish<true><<<fg, QB_BLOCK, 0, st>>>(S, B, P);
   } else {
     k_wf_trace<false><<<grid, QB_BLOCK, 0, st>>>(S, B, P);
+    k_redo_detect<false><<<148 * 8, QB_BLOCK, 0, st>>>(S, B, P);
+    k_redo_exact<false><<<148, QB_BLOCK, 0, st>>>(S, B, P);
     k_wf_finish<false><<<fg, QB_BLOCK, 0, st>>>(S, B, P);
   }
 }
@@ -409,16 +517,34 @@ static int flat_grid(size_t n)
   if (g < 1) g = 1;
   return (int) g;
 }
-// scratch: 1 + 8 * n words (work cursor, then two float4 records per ray), zero the cursor before the call
-size_t trace_rays_scratch_bytes(size_t n) { return 16 + 32 * n; }
+__global__ void __launch_bounds__(QB_BLOCK) k_redo_detect_rays(const DScene S, RayBufClosestIO io)
+{
+  if (*io.Q.count == 0u) return;
+  redo_detect(S, io, io.Q);
+}
+__global__ void __launch_bounds__(QB_BLOCK, QB_MIN_BLOCKS) k_redo_exact_rays(const DScene S, RayBufClosestIO base, unsigned long long *stats)
+{
+  __shared__ uint32_t s_stack[QB_STACK * QB_BLOCK];
+  const uint32_t n = min(*base.Q.count, base.Q.cap);
+  if (n == 0u) return;
+  TraceCounters cnt = {0, 0, 0};
+  RedoIO<RayBufClosestIO> io{base, base.Q, n};
+  traverse_pool<false>(S, io, s_stack, cnt);
+  flush_counters(stats, cnt);
+}
+// scratch: a 16-byte header (work cursor, cull-check count, cull-check cursor), two float4 records per ray, then the
+// cull-check queue (one uint4 per ray); the header is zeroed by the launch
+size_t trace_rays_scratch_bytes(size_t n) { return 16 + 48 * n; }
 void launch_trace_closest_rays(const DScene &S, const qgRay *rays, size_t n, qgHit *out, unsigned long long *stats, void *scratch,
                                cudaStream_t st)
 {
   uint32_t *cur = (uint32_t *) scratch;
   float4 *r0 = (float4 *) ((char *) scratch + 16), *r1 = r0 + n;
   cudaMemsetAsync(cur, 0, 16, st);
-  RayBufClosestIO io{rays, (uint32_t) n, cur, r0, r1};
+  RayBufClosestIO io{rays, (uint32_t) n, cur, r0, r1, RedoQueue{(uint4 *) (r1 + n), (uint32_t) n, cur + 1, cur + 2}};
   k_trace_closest_rays<<<flat_grid(n), QB_BLOCK, 0, st>>>(S, io, stats);
+  k_redo_detect_rays<<<148 * 8, QB_BLOCK, 0, st>>>(S, io);
+  k_redo_exact_rays<<<148, QB_BLOCK, 0, st>>>(S, io, stats);
   k_finish_rays<<<flat_grid(n), QB_BLOCK, 0, st>>>(S, rays, (uint32_t) n, r0, r1, out);
 }
 void launch_trace_any_rays(const DScene &S, const float *rays6, const float *tmax, size_t n, uint8_t *occ, unsigned long long *stats,

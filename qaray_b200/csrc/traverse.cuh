@@ -198,7 +198,9 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
       if (s_next && k > 0 && cull_state == 1) {
         // the cull dropped boxes and the mesh produced no hit inside its own box: repeat it exactly as the reference walks it
         cull_state = 0;
-        if (!(h.z <= z_sane)) {
+        // closest-hit rays of the wavefront hand the check to k_redo_detect / k_redo_exact (trace_kernels.cu) and go on: a
+        // single lane repeating a whole mesh costs up to ~30 ms, and some sample ranges hold a few dozen such rays
+        if (!(h.z <= z_sane) && (ANY || !io.defer(idx, k - 1, z_entry))) {
           redo = true;
           cull_state = 2;
           h.z = z_entry;
@@ -226,7 +228,7 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
             const DMesh *m = &S.meshes[__ldg(&nd->mesh)];
             if (__ldg(&m->num_faces) != 0u && mesh_box_hit(m, r, h.z, mesh_exit, drcp)) {
               cur = __ldg(&m->root_ref);
-              cull_state = 0;
+              cull_state = io.exact() ? 2 : 0;
               z_entry = h.z;
               {
                 const V3 ext = v3(__ldg(&m->bmax[0]) - __ldg(&m->bmin[0]), __ldg(&m->bmax[1]) - __ldg(&m->bmin[1]),
@@ -259,8 +261,9 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
         const uint32_t my = base + (uint32_t) __popc(m_fetch & lt_mask);
         float tmax = QB_BIGFLOAT;
         Ray3 c;
-        if (my < n && io.load(my, c, tmax)) {
-          idx = my;
+        const uint32_t ray = my < n ? io.map(my) : my;
+        if (my < n && io.load(ray, c, tmax)) {
+          idx = ray;
           c0 = to_node(root, c);
           h.z = tmax; h.k = -1; h.slot = -1; h.tex_k = -1; h.tex_slot = -1; h.tex_t = 0.f; h.last_tri = -1;
           k = 0; sp = 0; cur = QB_REF_EMPTY; obj_slot = -1; uv_slot = -1;

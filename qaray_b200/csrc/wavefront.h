@@ -32,7 +32,9 @@ namespace qb {
 #define QB_CNT_FETCH_SHADOW 64
 #define QB_CNT_AREA 80         // [80 .. 95] n_area[d]: (hit, area light) groups queued by shade(d)
 #define QB_CNT_FETCH_AREA 96   // [96 .. 111] work-fetch cursor of the area-light shadow kernel
-#define QB_CNT_WORDS 112
+#define QB_CNT_REDO 112        // [112 .. 127] closest-hit rays of trace(d) whose culled mesh walk must be checked (k_redo_detect)
+#define QB_CNT_FETCH_REDO 128  // [128 .. 143] work-fetch cursor of k_redo_exact
+#define QB_CNT_WORDS 144
 
 // area lights (PointLight / SpotLight with size > 0.01, src/lights/lights.cpp:50-65,84-101): shadow samples per group
 #define QB_MAT_BINS 256        // material sort: bin 0 = miss, 1 = no material / MultiMtl out of range, 2 + i = material i
@@ -66,6 +68,9 @@ struct WfBuffers {
   float4 *a2;       // contribution.rgb per unit of the light's visibility estimate
   uint32_t *amask;  // 2 words per group: bit s = shadow sample s reached the light
   uint32_t area_capacity;
+  // deferred checks of the degenerate-axis cull (traverse.cuh): {ray index, object, z at mesh entry (bits), flag}
+  uint4 *redo;
+  uint32_t redo_capacity;
   // material sort of the shade queue (optional): permutation and the per-material bins / offsets
   uint32_t *perm;      // capacity entries
   uint32_t *mat_bins;  // 2 * QB_MAT_BINS: counts, then running offsets
