@@ -168,12 +168,18 @@ template <class IO> __device__ __forceinline__ void redo_detect(const DScene &S,
     const DMesh *m = &S.meshes[__ldg(&S.nodes[__ldg(&S.obj_node[k])].mesh)];
     const uint32_t first = __ldg(&m->face_base), count = __ldg(&m->num_faces);  // triangle slots of a mesh = its face range
     const float z_entry = __uint_as_float(ent.z);
+    // Only a hit beyond the mesh box matters: a hit inside it lies in boxes the ray reaches, which the cull never drops, so
+    // the culled walk has tested it already (or the reference's own strict slab test skips its box, e.g. a flat one)
+    float mesh_exit = 0.f;
+    V3 drcp;
+    if (!mesh_box_hit(m, r, z_entry, mesh_exit, drcp)) continue;
+    const float t_box = mesh_exit * 1.001f;
     bool any = false;
     for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < count; t += gridDim.x * blockDim.x) {
       const DTri *tp = &S.tris[first + t];
       const float4 ta = __ldg(&tp->a), tb = __ldg(&tp->b), tc = __ldg(&tp->c), td = __ldg(&tp->d);
       float tt;
-      any = any || tri_accept(r, z_entry, xyz(ta), xyz(tb), xyz(tc), v3(ta.w, tb.w, tc.w), td.x, __float_as_int(td.y), tt);
+      if (tri_accept(r, z_entry, xyz(ta), xyz(tb), xyz(tc), v3(ta.w, tb.w, tc.w), td.x, __float_as_int(td.y), tt) && tt > t_box) any = true;
     }
     if (any) Q.q[e].w = 1u;
   }
