@@ -227,7 +227,10 @@ def run_b200_arm(args):
     accum = torch.zeros(npix * 4, dtype=torch.float32, device=dev)
     depth = torch.zeros(npix, dtype=torch.float32, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
-    stream = torch.cuda.current_stream()
+    # an explicit stream: a NULL stream handle means "the scene's own stream" to the library, which is not ordered with torch's
+    # legacy default stream (the zero_() calls below)
+    stream = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(stream)
     sptr = C.c_void_p(stream.cuda_stream)
     my = params(rank * args.spp, (rank + 1) * args.spp)
     # host output planes (pinned) for the e2e path

@@ -223,7 +223,10 @@ int qg_render(qgScene *scene, const qgRenderParams *params, float *rgb_mean, uin
 /* Shard render into a DEVICE accumulation buffer accum[W*H*4] = {sum R, sum G, sum B, sum weight} (+=) and
  * depth[W*H] (written where this shard owns sample 0, else left untouched). For the multi-GPU path: every rank
  * accumulates its tile/sample shard, the buffers are summed by one NCCL reduce (replacing the MPI_Send/Recv
- * gather of src/renderers/Renderer_MPI.cpp:142-207), and the root resolves. stream = cudaStream_t or NULL. */
+ * gather of src/renderers/Renderer_MPI.cpp:142-207), and the root resolves. stream = cudaStream_t, or NULL for the scene's own non-blocking
+ * stream (NOT ordered with the legacy default stream: synchronise d_accum / d_depth producers first). The any-hit kernels
+ * of each depth run on a second, library-owned stream that forks from and joins `stream` inside the call; the call returns
+ * after the whole render has finished on the device. */
 int qg_render_accumulate(qgScene *scene, const qgRenderParams *params, float *d_accum, float *d_depth, void *stream,
                          qgRenderStats *stats);
 /* accum (device) -> mean, sRGB, clamp, round (renderer.cpp:348-361). Host outputs as in qg_render. */

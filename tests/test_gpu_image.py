@@ -83,3 +83,33 @@ def test_tile_shards_union_equals_whole_frame():
         assert np.array_equal(depth[mask == 1], whole[2][mask == 1])
     assert (cover == 1).all()
     assert np.allclose(acc, whole[0], rtol=1e-5, atol=1e-6)
+
+
+def test_no_sample_shard_is_pathologically_slow():
+    """Sample shards of the BASELINE scene do the same amount of work, so their device times must agree. Guards the exact
+    check of the degenerate-axis cull (deviation 1): when a lane repeated a whole mesh by itself, shards 1, 4
+    and 5 of a 512-spp tower frame took twice as long as the others (a few rays, ~30 ms each)."""
+    import ctypes as C
+
+    import torch
+
+    from qaray_b200 import capi
+    lib = capi.load()
+    capi.check(lib, lib.qg_init(0))
+    h = C.c_void_p()
+    capi.check(lib, lib.qg_scene_load_xml(os.fsencode(scene_xml("trc_scene_tower")), os.fsencode(ASSETS), C.byref(h)))
+    info = capi.SceneInfo()
+    capi.check(lib, lib.qg_scene_info(h, C.byref(info)))
+    W, H = info.camera.width, info.camera.height
+    acc = torch.zeros(W * H * 4, dtype=torch.float32, device="cuda")
+    st = capi.RenderStats()
+    spp, shards, ms = 64, 8, []
+    for r in [0] + list(range(shards)):  # the first call allocates: run shard 0 twice, keep the second
+        p = capi.RenderParams(spp * shards, 5, 1, 0x5EED, W, H, 0, 1, r * spp, (r + 1) * spp, 0, 0)
+        acc.zero_()
+        torch.cuda.synchronize()
+        capi.check(lib, lib.qg_render_accumulate(h, C.byref(p), C.c_void_p(acc.data_ptr()), None, None, C.byref(st)))
+        ms.append(st.device_ms)
+    lib.qg_scene_destroy(h)
+    ms = np.array(ms[1:])
+    assert ms.max() <= 1.25 * np.median(ms), "shard device times (ms): %s" % np.round(ms, 1)
