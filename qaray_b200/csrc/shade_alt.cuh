@@ -90,11 +90,18 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade_alt(const DScene S, const
   const float norm_di = S.num_lights > 0 ? 1.f / (float) S.num_lights : 1.f;
   // MtlBlinn_MonteCarloGI.cpp:176-178: 10 hemisphere samples at the camera-visible hit, 1 below
   const int num_mc = CLS == QG_CLASS_MONTECARLOGI ? ((P.max_bounce - 1 - bounce_count >= 0) ? 1 : 10) : 0;
+  uint32_t w_next = 0, w_end = 0;  // the warp's reserved slice of the queue: one cursor atomic per QB_SHADE_CHUNK paths
   for (;;) {
-    uint32_t base = 0;
-    if (lane == 0) base = atomicAdd(&B.counters[QB_CNT_FETCH_SHADE + d], 32u);
-    base = __shfl_sync(0xFFFFFFFFu, base, 0);
-    if (base >= n) break;
+    if (w_next >= w_end) {
+      uint32_t cbase = 0;
+      if (lane == 0) cbase = atomicAdd(&B.counters[QB_CNT_FETCH_SHADE + d], (uint32_t) QB_SHADE_CHUNK);
+      cbase = __shfl_sync(0xFFFFFFFFu, cbase, 0);
+      if (cbase >= n) break;
+      w_next = cbase;
+      w_end = min(cbase + (uint32_t) QB_SHADE_CHUNK, n);
+    }
+    const uint32_t base = w_next;
+    w_next += 32u;
     // material-sorted order (qgRenderParams.sort_by_material): queue position -> path index through the permutation
     // k_mat_scatter built; lanes past the end get n (no work)
     const uint32_t idx = base + lane < n ? (P.sort_mat ? B.perm[base + lane] : base + lane) : n;

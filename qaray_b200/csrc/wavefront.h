@@ -37,6 +37,9 @@ namespace qb {
 #define QB_CNT_WORDS 144
 
 // area lights (PointLight / SpotLight with size > 0.01, src/lights/lights.cpp:50-65,84-101): shadow samples per group
+#ifndef QB_SHADE_CHUNK
+#define QB_SHADE_CHUNK 256       // paths a shade warp reserves per cursor atomic (multiple of 32)
+#endif
 #define QB_MAT_BINS 256        // material sort: bin 0 = miss, 1 = no material / MultiMtl out of range, 2 + i = material i
 #define QB_AREA_SPP_MIN 16     // GenLight::shadow_spp_min (lights.cpp:16)
 #define QB_AREA_SPP_MAX 64     // GenLight::shadow_spp_max (lights.cpp:17)
