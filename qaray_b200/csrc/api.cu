@@ -403,6 +403,9 @@ int ensure_wf(qgScene *sc, uint32_t capacity, bool carry_diff = false)
   for (void *p : sc->wf_allocs) cudaFree(p);
   sc->wf_allocs.clear();
   sc->wf_capacity = 0;
+  // room for the dead entries of k_wf_shade's output reservations: at most one QB_OUT_CHUNK tail per shade warp and queue
+  const uint32_t requested = capacity;
+  capacity += (uint32_t) wf_shade_grid() * (QB_BLOCK / 32) * QB_OUT_CHUNK;
   WfBuffers &B = sc->wf;
   memset(&B, 0, sizeof B);
   auto alloc4 = [&](float4 **p, size_t n) -> cudaError_t {
@@ -455,7 +458,7 @@ int ensure_wf(qgScene *sc, uint32_t capacity, bool carry_diff = false)
   B.stats = sc->stats.p;
   B.capacity = capacity;
   B.shadow_capacity = (uint32_t) std::min<size_t>(shadow_cap, 0xFFFFFFFFu);
-  sc->wf_capacity = capacity;
+  sc->wf_capacity = requested;
   return QG_OK;
 }
 

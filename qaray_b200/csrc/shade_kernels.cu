@@ -200,6 +200,31 @@ __device__ __forceinline__ void push_area_group(const WfBuffers &B, int d, int l
   B.a2[q] = make_float4(contrib.x, contrib.y, contrib.z, 0.f);
 }
 
+// Output reservation of a shade warp. Every push used to cost one atomic on the queue's counter — one address for the whole
+// grid, and the SASS page showed the kernel waiting on exactly those (the SHFL after each leader atomic). A warp now reserves
+// QB_OUT_CHUNK slots at a time and hands them out itself; a push that does not fit takes the tail of the old reservation and
+// the head of a new one, so the only unused slots are each warp's last tail, which it fills with dead entries at the end
+// (path: slot -1, shadow: tmax -1; the consumers skip them, QB_CNT_HOLES_* keeps the ray statistics exact).
+struct OutRes {
+  uint32_t next, end;
+};
+__device__ __forceinline__ uint32_t res_take(OutRes &R, uint32_t *counter, int lane, uint32_t m, uint32_t rank)
+{
+  const uint32_t left = R.end - R.next;
+  if (m > left) {
+    uint32_t nb = 0;
+    if (lane == 0) nb = atomicAdd(counter, (uint32_t) QB_OUT_CHUNK);
+    nb = __shfl_sync(0xFFFFFFFFu, nb, 0);
+    const uint32_t q = rank < left ? R.next + rank : nb + (rank - left);
+    R.next = nb + (m - left);
+    R.end = nb + (uint32_t) QB_OUT_CHUNK;
+    return q;
+  }
+  const uint32_t q = R.next + rank;
+  R.next += m;
+  return q;
+}
+
 __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade(const DScene S, const WfBuffers B, const WfParams P)
 {
   const int d = P.depth;
@@ -209,6 +234,7 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade(const DScene S, const WfB
   const uint32_t lt_mask = (1u << lane) - 1u;
   const int pb = d & 1, nb = pb ^ 1;
   const float color_luma_threshold = 0.00001f;
+  OutRes rp = {0u, 0u}, rs = {0u, 0u};  // reservations in the path queue of depth d + 1 and in the shadow queue of depth d
   uint32_t w_next = 0, w_end = 0;  // the warp's reserved slice of the queue: one cursor atomic per QB_SHADE_CHUNK paths
   for (;;) {
     if (w_next >= w_end) {
@@ -268,7 +294,8 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade(const DScene S, const WfB
         rng.n = packed >> 8;
         flags = packed & 0xFFu;
         absorb_prev = v3(e.x, e.y, e.z);
-        if (node < 0) accum_add(P.accum, slot, T * sample_environment(S, ray_dir));  // ComputeSecondaryRay miss (:250)
+        valid = slot >= 0;  // slot -1: a dead entry (unused tail of a shade warp's reservation)
+        if (node < 0 && valid) accum_add(P.accum, slot, T * sample_environment(S, ray_dir));  // ComputeSecondaryRay miss (:250)
       }
       if (valid && node >= 0) {
         const float4 h1 = B.h1[idx], h2 = B.h2[idx], h3 = B.h3[idx];
@@ -396,11 +423,8 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade(const DScene S, const WfB
       }
       const uint32_t mask = __ballot_sync(0xFFFFFFFFu, push);
       if (mask) {
-        uint32_t qbase = 0;
-        if (lane == 0) qbase = atomicAdd(&B.counters[QB_CNT_SHADOW + d], (uint32_t) __popc(mask));
-        qbase = __shfl_sync(0xFFFFFFFFu, qbase, 0);
-        if (push) {
-          const uint32_t q = qbase + __popc(mask & lt_mask);
+        const uint32_t q = res_take(rs, &B.counters[QB_CNT_SHADOW + d], lane, (uint32_t) __popc(mask), (uint32_t) __popc(mask & lt_mask));
+        if (push && q < B.shadow_capacity) {
           B.s0[q] = make_float4(p.x, p.y, p.z, sdir.x);
           B.s1[q] = make_float4(sdir.y, sdir.z, tmax, __int_as_float(slot));
           B.s2[q] = make_float4(contrib.x, contrib.y, contrib.z, 0.f);
@@ -411,11 +435,8 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade(const DScene S, const WfB
     // ---- queue compaction: surviving paths go to the state buffer of depth d+1
     const uint32_t amask = __ballot_sync(0xFFFFFFFFu, alive);
     if (amask) {
-      uint32_t qbase = 0;
-      if (lane == 0) qbase = atomicAdd(&B.counters[QB_CNT_PATHS + d + 1], (uint32_t) __popc(amask));
-      qbase = __shfl_sync(0xFFFFFFFFu, qbase, 0);
-      if (alive) {
-        const uint32_t q = qbase + __popc(amask & lt_mask);
+      const uint32_t q = res_take(rp, &B.counters[QB_CNT_PATHS + d + 1], lane, (uint32_t) __popc(amask), (uint32_t) __popc(amask & lt_mask));
+      if (alive && q < B.capacity) {
         const V3 nd = normalize(next_dir);  // DiffRay::Normalize in ComputeSecondaryRay (:235-236)
         B.ps0[nb][q] = make_float4(p.x, p.y, p.z, nd.x);
         B.ps1[nb][q] = make_float4(nd.y, nd.z, __int_as_float(slot), __uint_as_float(rng.key));
@@ -423,6 +444,22 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade(const DScene S, const WfB
         B.ps3[nb][q] = make_float4(next_absorb.x, next_absorb.y, next_absorb.z, 0.f);
       }
     }
+  }
+  // the unused tails of this warp's reservations become dead entries
+  for (uint32_t q = rp.next + (uint32_t) lane; q < min(rp.end, B.capacity); q += 32u) {
+    B.ps0[nb][q] = make_float4(0.f, 0.f, 0.f, 0.f);
+    B.ps1[nb][q] = make_float4(1.f, 0.f, __int_as_float(-1), 0.f);
+    B.ps2[nb][q] = make_float4(0.f, 0.f, 0.f, 0.f);
+    B.ps3[nb][q] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  for (uint32_t q = rs.next + (uint32_t) lane; q < min(rs.end, B.shadow_capacity); q += 32u) {
+    B.s0[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+    B.s1[q] = make_float4(1.f, 0.f, -1.f, 0.f);
+    B.s2[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  if (lane == 0) {
+    if (rp.end > rp.next) atomicAdd(&B.counters[QB_CNT_HOLES_PATHS + d + 1], rp.end - rp.next);
+    if (rs.end > rs.next) atomicAdd(&B.counters[QB_CNT_HOLES_SHADOW + d], rs.end - rs.next);
   }
 }
 
@@ -626,8 +663,8 @@ __global__ void k_wf_stats(const uint32_t *__restrict__ counters, unsigned long 
 {
   unsigned long long closest = 0, shadow = 0;
   for (int d = 0; d <= max_bounce; ++d) {
-    if (d >= 1) closest += counters[QB_CNT_PATHS + d];
-    shadow += counters[QB_CNT_SHADOW + d] + (unsigned long long) counters[QB_CNT_AREA + d] * QB_AREA_SPP_MAX;
+    if (d >= 1) closest += counters[QB_CNT_PATHS + d] - counters[QB_CNT_HOLES_PATHS + d];
+    shadow += counters[QB_CNT_SHADOW + d] - counters[QB_CNT_HOLES_SHADOW + d] + (unsigned long long) counters[QB_CNT_AREA + d] * QB_AREA_SPP_MAX;
   }
   stats[0] += closest;
   stats[1] += shadow;

@@ -98,6 +98,12 @@ struct WfClosestIO {
       primary_ray(P, i, j, s, c, x, y);
     } else {
       const float4 a = B.ps0[P.depth & 1][idx], b = B.ps1[P.depth & 1][idx];
+      if (__float_as_int(b.z) < 0) {  // dead entry (shade_kernels.cu, OutRes): report a miss, trace nothing
+        HitRec m;
+        m.z = QB_BIGFLOAT; m.k = -1; m.slot = -1; m.tex_k = -1; m.tex_slot = -1; m.tex_t = 0.f; m.last_tri = -1;
+        put_rec(B.h1, B.h2, idx, m);
+        return false;
+      }
       c.p = v3(a.x, a.y, a.z);
       c.d = v3(a.w, b.x, b.y);
     }
@@ -122,7 +128,7 @@ struct WfShadowIO {
     c.p = v3(a.x, a.y, a.z);
     c.d = v3(a.w, b.x, b.y);
     tmax = b.z;
-    return true;
+    return tmax >= 0.f;  // tmax -1: a dead entry (shade_kernels.cu, OutRes)
   }
   __device__ void store(uint32_t, const HitRec &) {}
   __device__ void store_any(uint32_t idx, bool occluded)

@@ -34,11 +34,16 @@ namespace qb {
 #define QB_CNT_FETCH_AREA 96   // [96 .. 111] work-fetch cursor of the area-light shadow kernel
 #define QB_CNT_REDO 112        // [112 .. 127] closest-hit rays of trace(d) whose culled mesh walk must be checked (k_redo_detect)
 #define QB_CNT_FETCH_REDO 128  // [128 .. 143] work-fetch cursor of k_redo_exact
-#define QB_CNT_WORDS 144
+#define QB_CNT_HOLES_PATHS 144  // [144 .. 159] dead entries in the path queue of depth d (unused tails of the shade warps' reservations)
+#define QB_CNT_HOLES_SHADOW 160 // [160 .. 175] dead entries in the shadow queue of depth d
+#define QB_CNT_WORDS 176
 
 // area lights (PointLight / SpotLight with size > 0.01, src/lights/lights.cpp:50-65,84-101): shadow samples per group
 #ifndef QB_SHADE_CHUNK
 #define QB_SHADE_CHUNK 256       // paths a shade warp reserves per cursor atomic (multiple of 32)
+#endif
+#ifndef QB_OUT_CHUNK
+#define QB_OUT_CHUNK 256         // queue slots a shade warp reserves per push atomic (k_wf_shade); multiple of 32
 #endif
 #define QB_MAT_BINS 256        // material sort: bin 0 = miss, 1 = no material / MultiMtl out of range, 2 + i = material i
 #define QB_AREA_SPP_MIN 16     // GenLight::shadow_spp_min (lights.cpp:16)
