@@ -28,18 +28,15 @@ struct AltChild {
 
 // warp-converged: every lane calls it; lanes with c.on append one path to the queue of depth d + 1
 __device__ __forceinline__ void push_child(const WfBuffers &B, const WfParams &P, int d, int lane, uint32_t lt_mask, V3 p, int slot,
-                                           const AltChild &c)
+                                           const AltChild &c, OutRes &rp)
 {
   // a child whose throughput is exactly zero can add nothing to the pixel: not traced (like zero-contribution shadow rays)
   const bool on = c.on && (c.T.x != 0.f || c.T.y != 0.f || c.T.z != 0.f);
   const uint32_t m = __ballot_sync(0xFFFFFFFFu, on);
   if (!m) return;
   const int nb = (d & 1) ^ 1;
-  uint32_t qbase = 0;
-  if (lane == 0) qbase = atomicAdd(&B.counters[QB_CNT_PATHS + d + 1], (uint32_t) __popc(m));
-  qbase = __shfl_sync(0xFFFFFFFFu, qbase, 0);
+  const uint32_t q = res_take(rp, &B.counters[QB_CNT_PATHS + d + 1], lane, (uint32_t) __popc(m), (uint32_t) __popc(m & lt_mask));
   if (!on) return;
-  const uint32_t q = qbase + __popc(m & lt_mask);
   if (q >= B.capacity) return;  // cannot happen: the wave size divides the capacity by the class's worst-case growth
   const V3 nd = normalize(c.dir);  // DiffRay::Normalize
   B.ps0[nb][q] = make_float4(p.x, p.y, p.z, nd.x);
@@ -90,6 +87,7 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade_alt(const DScene S, const
   const float norm_di = S.num_lights > 0 ? 1.f / (float) S.num_lights : 1.f;
   // MtlBlinn_MonteCarloGI.cpp:176-178: 10 hemisphere samples at the camera-visible hit, 1 below
   const int num_mc = CLS == QG_CLASS_MONTECARLOGI ? ((P.max_bounce - 1 - bounce_count >= 0) ? 1 : 10) : 0;
+  OutRes rp = {0u, 0u}, rs = {0u, 0u};  // reservations in the path queue of depth d + 1 and the shadow queue of depth d (k_wf_shade)
   uint32_t w_next = 0, w_end = 0;  // the warp's reserved slice of the queue: one cursor atomic per QB_SHADE_CHUNK paths
   for (;;) {
     if (w_next >= w_end) {
@@ -162,7 +160,8 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade_alt(const DScene S, const
           rx.p = v3(f.x, f.y, f.z); rx.d = v3(f.w, g.x, g.y);
           ry.p = v3(g.z, g.w, h.x); ry.d = v3(h.y, h.z, h.w);
         }
-        if (node < 0) accum_add(P.accum, slot, T * sample_environment(S, rc.d));
+        valid = slot >= 0;  // slot -1: a dead entry (unused tail of a shade warp's reservation)
+        if (node < 0 && valid) accum_add(P.accum, slot, T * sample_environment(S, rc.d));
       }
       if (valid && node >= 0) {
         const float4 h1 = B.h1[idx], h2 = B.h2[idx], h3 = B.h3[idx];
@@ -382,11 +381,8 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade_alt(const DScene S, const
       }
       const uint32_t mask = __ballot_sync(0xFFFFFFFFu, push);
       if (mask) {
-        uint32_t qbase = 0;
-        if (lane == 0) qbase = atomicAdd(&B.counters[QB_CNT_SHADOW + d], (uint32_t) __popc(mask));
-        qbase = __shfl_sync(0xFFFFFFFFu, qbase, 0);
+        const uint32_t q = res_take(rs, &B.counters[QB_CNT_SHADOW + d], lane, (uint32_t) __popc(mask), (uint32_t) __popc(mask & lt_mask));
         if (push) {
-          const uint32_t q = qbase + __popc(mask & lt_mask);
           if (q < B.shadow_capacity) {
             B.s0[q] = make_float4(p.x, p.y, p.z, sdir.x);
             B.s1[q] = make_float4(sdir.y, sdir.z, tmax, __int_as_float(slot));
@@ -398,8 +394,8 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade_alt(const DScene S, const
 
     // ---- children ----------------------------------------------------------------------------------------------------
     if (!BRANCHING) c0.n = rng.n;
-    push_child(B, P, d, lane, lt_mask, p, slot, c0);
-    if (BRANCHING) push_child(B, P, d, lane, lt_mask, p, slot, c1);
+    push_child(B, P, d, lane, lt_mask, p, slot, c0, rp);
+    if (BRANCHING) push_child(B, P, d, lane, lt_mask, p, slot, c1, rp);
     if (CLS == QG_CLASS_MONTECARLOGI) {
       // MtlBlinn_MonteCarloGI.cpp:197-257: cos-weighted hemisphere samples about N, each weighted
       // (cosNL * Ks * cosNH^gloss + Kd) / numSampleMC; traced as DiffRay(p, dir) (no differentials), no absorption
@@ -424,10 +420,11 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade_alt(const DScene S, const
           cm.key = r2.key;
           cm.n = r2.n;
         }
-        push_child(B, P, d, lane, lt_mask, p, slot, cm);
+        push_child(B, P, d, lane, lt_mask, p, slot, cm, rp);
       }
     }
   }
+  res_flush(B, d, lane, rp, rs);
 }
 
 }  // namespace qb

@@ -225,6 +225,27 @@ __device__ __forceinline__ uint32_t res_take(OutRes &R, uint32_t *counter, int l
   return q;
 }
 
+// the unused tails of a warp's reservations become dead entries (end of a shade kernel)
+__device__ __forceinline__ void res_flush(const WfBuffers &B, int d, int lane, const OutRes &rp, const OutRes &rs)
+{
+  const int nb = (d & 1) ^ 1;
+  for (uint32_t q = rp.next + (uint32_t) lane; q < min(rp.end, B.capacity); q += 32u) {
+    B.ps0[nb][q] = make_float4(0.f, 0.f, 0.f, 0.f);
+    B.ps1[nb][q] = make_float4(1.f, 0.f, __int_as_float(-1), 0.f);
+    B.ps2[nb][q] = make_float4(0.f, 0.f, 0.f, 0.f);
+    B.ps3[nb][q] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  for (uint32_t q = rs.next + (uint32_t) lane; q < min(rs.end, B.shadow_capacity); q += 32u) {
+    B.s0[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+    B.s1[q] = make_float4(1.f, 0.f, -1.f, 0.f);
+    B.s2[q] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  if (lane == 0) {
+    if (rp.end > rp.next) atomicAdd(&B.counters[QB_CNT_HOLES_PATHS + d + 1], rp.end - rp.next);
+    if (rs.end > rs.next) atomicAdd(&B.counters[QB_CNT_HOLES_SHADOW + d], rs.end - rs.next);
+  }
+}
+
 __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade(const DScene S, const WfBuffers B, const WfParams P)
 {
   const int d = P.depth;
@@ -445,22 +466,7 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade(const DScene S, const WfB
       }
     }
   }
-  // the unused tails of this warp's reservations become dead entries
-  for (uint32_t q = rp.next + (uint32_t) lane; q < min(rp.end, B.capacity); q += 32u) {
-    B.ps0[nb][q] = make_float4(0.f, 0.f, 0.f, 0.f);
-    B.ps1[nb][q] = make_float4(1.f, 0.f, __int_as_float(-1), 0.f);
-    B.ps2[nb][q] = make_float4(0.f, 0.f, 0.f, 0.f);
-    B.ps3[nb][q] = make_float4(0.f, 0.f, 0.f, 0.f);
-  }
-  for (uint32_t q = rs.next + (uint32_t) lane; q < min(rs.end, B.shadow_capacity); q += 32u) {
-    B.s0[q] = make_float4(0.f, 0.f, 0.f, 0.f);
-    B.s1[q] = make_float4(1.f, 0.f, -1.f, 0.f);
-    B.s2[q] = make_float4(0.f, 0.f, 0.f, 0.f);
-  }
-  if (lane == 0) {
-    if (rp.end > rp.next) atomicAdd(&B.counters[QB_CNT_HOLES_PATHS + d + 1], rp.end - rp.next);
-    if (rs.end > rs.next) atomicAdd(&B.counters[QB_CNT_HOLES_SHADOW + d], rs.end - rs.next);
-  }
+  res_flush(B, d, lane, rp, rs);
 }
 
 }  // namespace qb
