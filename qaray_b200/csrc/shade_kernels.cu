@@ -282,7 +282,12 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade(const DScene S, const WfB
     Rng rng = {0u, 0u};
 
     if (idx < n) {
+      // every record of the path is requested up front: the three dependent round trips (h0 -> path state -> h1..h3) were
+      // the kernel's top stalls once the queue atomics were gone (profiles/README.md)
       const float4 h0 = B.h0[idx];
+      const float4 h1 = B.h1[idx], h2 = B.h2[idx], h3 = B.h3[idx];
+      float4 sa = make_float4(0.f, 0.f, 0.f, 0.f), sb = sa, sc4 = sa, se = sa;
+      if (d > 0) { sa = B.ps0[pb][idx]; sb = B.ps1[pb][idx]; sc4 = B.ps2[pb][idx]; se = B.ps3[pb][idx]; }
       const int node = __float_as_int(h0.y);
       V3 ray_dir;
       V3 absorb_prev = v3(0.f);
@@ -306,7 +311,7 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade(const DScene S, const WfB
           }
         }
       } else {
-        const float4 a = B.ps0[pb][idx], b = B.ps1[pb][idx], c = B.ps2[pb][idx], e = B.ps3[pb][idx];
+        const float4 a = sa, b = sb, c = sc4, e = se;
         ray_dir = v3(a.w, b.x, b.y);
         slot = __float_as_int(b.z);
         rng.key = __float_as_uint(b.w);
@@ -319,7 +324,6 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade(const DScene S, const WfB
         if (node < 0 && valid) accum_add(P.accum, slot, T * sample_environment(S, ray_dir));  // ComputeSecondaryRay miss (:250)
       }
       if (valid && node >= 0) {
-        const float4 h1 = B.h1[idx], h2 = B.h2[idx], h3 = B.h3[idx];
         const float z = h0.x;
         const int mtl_id = __float_as_int(h0.z);
         const int hflags = __float_as_int(h0.w);
