@@ -500,7 +500,10 @@ int wf_shadow_grid() { static int g = persistent_grid((const void *) k_wf_shadow
 void launch_wf_trace(const DScene &S, const WfBuffers &B, const WfParams &P, int grid, cudaStream_t st)
 {
   // traversal by the lane pool, then the hit attributes by full warps
-  const int fg = 148 * 8;
+  // grid-stride kernels sized to what is resident at once (96 registers: 5 blocks / SM): a larger grid runs its last blocks
+  // alone at low occupancy
+  static const int fg_primary = persistent_grid((const void *) k_wf_finish<true>), fg_secondary = persistent_grid((const void *) k_wf_finish<false>);
+  const int fg = P.depth == 0 ? fg_primary : fg_secondary;
   if (P.depth == 0) {
     k_wf_trace<true><<<grid, QB_BLOCK, 0, st>>>(S, B, P);
     k_redo_detect<true><<<148 * 8, QB_BLOCK, 0, st>>>(S, B, P);
