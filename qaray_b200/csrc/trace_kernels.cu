@@ -79,7 +79,7 @@ struct WfClosestIO {
   __device__ uint32_t count() const { return n; }
   __device__ uint32_t *cursor() { return &B.counters[QB_CNT_FETCH_TRACE + P.depth]; }
   __device__ uint32_t map(uint32_t q) const { return q; }
-  __device__ bool exact() const { return false; }
+  __device__ bool exact(uint32_t, int) const { return false; }  // true: walk this mesh with the degenerate-axis cull off
   // hand a (ray, mesh) whose culled walk dropped boxes and found nothing to the redo kernels; false when the queue is full
   __device__ bool defer(uint32_t idx, int k, float z_entry) const
   {
@@ -120,7 +120,7 @@ struct WfShadowIO {
   __device__ uint32_t count() const { return n; }
   __device__ uint32_t *cursor() { return &B.counters[QB_CNT_FETCH_SHADOW + P.depth]; }
   __device__ uint32_t map(uint32_t q) const { return q; }                 // queue position -> ray index
-  __device__ bool exact() const { return false; }                          // true: degenerate-axis cull off for every mesh
+  __device__ bool exact(uint32_t, int) const { return false; }  // true: walk this mesh with the degenerate-axis cull off
   __device__ bool defer(uint32_t, int, float) const { return false; }      // false: the lane repeats the mesh itself
   __device__ bool load(uint32_t idx, Ray3 &c, float &tmax)
   {
@@ -158,8 +158,8 @@ __global__ void __launch_bounds__(QB_BLOCK, QB_MIN_BLOCKS) k_wf_trace(const DSce
 // every box such a ray's two regular axes cross and can accept a rounding-noise hit there (t ~ 1e6 on a triangle the ray
 // never touches). k_redo_detect decides with the whole GPU whether ANY triangle of the mesh accepts the ray — a superset of
 // what the reference tests, so "none" proves the stored record exact (the usual outcome). A pair with an accepting triangle
-// is re-traced by k_redo_exact with the cull off from the first object on, i.e. exactly as the reference walks it, and its
-// record is overwritten.
+// is re-traced by k_redo_exact with the cull off for the flagged meshes, i.e. as the reference walks them, and its record
+// is overwritten.
 template <class IO> __device__ __forceinline__ void redo_detect(const DScene &S, IO &io, const RedoQueue &Q)
 {
   const uint32_t n = min(*Q.count, Q.cap);
@@ -199,8 +199,18 @@ struct RedoIO {
   __device__ uint32_t count() const { return n; }
   __device__ uint32_t *cursor() { return Q.fetch; }
   __device__ uint32_t map(uint32_t q) const { return Q.q[q].w ? Q.q[q].x : 0xFFFFFFFFu; }
-  __device__ bool exact() const { return true; }
-  __device__ bool defer(uint32_t, int, float) const { return false; }
+  // the cull is off only for the (ray, mesh) pairs k_redo_detect flagged. Every other pair that drops boxes and finds
+  // nothing in this pass did so in the first pass too (h.z can only be smaller now) and was cleared there against a
+  // larger z, so it needs no second check: defer() swallows it
+  __device__ bool exact(uint32_t idx, int k) const
+  {
+    for (uint32_t e = 0; e < n; ++e) {
+      const uint4 ent = Q.q[e];
+      if (ent.x == idx && (int) ent.y == k && ent.w) return true;
+    }
+    return false;
+  }
+  __device__ bool defer(uint32_t, int, float) const { return true; }
   __device__ bool load(uint32_t idx, Ray3 &c, float &tmax) { return idx != 0xFFFFFFFFu && base.load(idx, c, tmax); }
   __device__ void store(uint32_t idx, const HitRec &h) { base.store(idx, h); }
   __device__ void store_any(uint32_t, bool) {}
@@ -296,7 +306,7 @@ struct WfAreaIO {
   __device__ uint32_t count() const { return n; }
   __device__ uint32_t *cursor() { return &B.counters[QB_CNT_FETCH_AREA + P.depth]; }
   __device__ uint32_t map(uint32_t q) const { return q; }                 // queue position -> ray index
-  __device__ bool exact() const { return false; }                          // true: degenerate-axis cull off for every mesh
+  __device__ bool exact(uint32_t, int) const { return false; }  // true: walk this mesh with the degenerate-axis cull off
   __device__ bool defer(uint32_t, int, float) const { return false; }      // false: the lane repeats the mesh itself
   __device__ bool load(uint32_t idx, Ray3 &c, float &tmax)
   {
@@ -383,7 +393,7 @@ struct RayBufClosestIO {
   __device__ uint32_t count() const { return n; }
   __device__ uint32_t *cursor() { return cur; }
   __device__ uint32_t map(uint32_t q) const { return q; }
-  __device__ bool exact() const { return false; }
+  __device__ bool exact(uint32_t, int) const { return false; }  // true: walk this mesh with the degenerate-axis cull off
   __device__ bool defer(uint32_t idx, int k, float z_entry) const { return redo_push(Q, idx, k, z_entry); }
   __device__ bool load(uint32_t idx, Ray3 &c, float &tmax)
   {
@@ -404,7 +414,7 @@ struct RayBufAnyIO {
   __device__ uint32_t count() const { return n; }
   __device__ uint32_t *cursor() { return cur; }
   __device__ uint32_t map(uint32_t q) const { return q; }                 // queue position -> ray index
-  __device__ bool exact() const { return false; }                          // true: degenerate-axis cull off for every mesh
+  __device__ bool exact(uint32_t, int) const { return false; }  // true: walk this mesh with the degenerate-axis cull off
   __device__ bool defer(uint32_t, int, float) const { return false; }      // false: the lane repeats the mesh itself
   __device__ bool load(uint32_t idx, Ray3 &c, float &tmax)
   {

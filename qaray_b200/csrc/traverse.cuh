@@ -228,7 +228,7 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
             const DMesh *m = &S.meshes[__ldg(&nd->mesh)];
             if (__ldg(&m->num_faces) != 0u && mesh_box_hit(m, r, h.z, mesh_exit, drcp)) {
               cur = __ldg(&m->root_ref);
-              cull_state = io.exact() ? 2 : 0;
+              cull_state = io.exact(idx, k - 1) ? 2 : 0;  // k was advanced above: k - 1 is this object
               z_entry = h.z;
               {
                 const V3 ext = v3(__ldg(&m->bmax[0]) - __ldg(&m->bmin[0]), __ldg(&m->bmax[1]) - __ldg(&m->bmin[1]),
