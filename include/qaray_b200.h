@@ -239,10 +239,51 @@ int qg_resolve(qgScene *scene, const qgRenderParams *params, const float *d_accu
  * all ranks must tile the frame exactly once per sample (tests/test_sharding.py). */
 int qg_shard_coverage(const qgCamera *camera, const qgRenderParams *params, uint16_t *counts);
 
+/* ---- multi-GPU: the reference's rank model (Renderer_MPI, src/renderers/Renderer_MPI.cpp) over NCCL ----------------------
+ * Every rank accumulates its shard of the frame — tiles k = r_t (mod G_t) of the reference's interleaved 4x4-tile rule
+ * (renderer.cpp:383-387) and the r_s-th of G_s equal sample ranges, G = G_t x G_s ranks, r = r_s * G_t + r_t — into a full-frame
+ * accumulation buffer; one ncclReduce(sum) per buffer to rank 0 replaces the MPI_Send / MPI_Recv / PlaceImage gather
+ * (Renderer_MPI.cpp:142-207). NCCL is bound when the first of these is called (dlopen libnccl.so.2); without it they fail
+ * with QG_ENODEVICE and everything above keeps working. */
+
+/* this rank's shard of `params` (which must describe the whole frame). tile_split = G_t: 1 = sample shards only,
+ * nranks = tile shards only (the reference's own rule). Needs no GPU. */
+int qg_shard_params(const qgRenderParams *params, int32_t rank, int32_t nranks, int32_t tile_split, qgRenderParams *out);
+
+/* One process per GPU (Renderer_MPI::Init, :33-55: MPI_Comm_rank / MPI_Comm_size). Rank 0 fills id[QG_COMM_ID_BYTES] and ships
+ * it to the other ranks by any means; every rank then joins on the device qg_init chose. */
+#define QG_COMM_ID_BYTES 128
+typedef struct qgComm qgComm;
+int qg_comm_unique_id(void *id);
+int qg_comm_create(const void *id, int rank, int nranks, qgComm **out);
+int qg_comm_info(const qgComm *comm, int32_t *rank, int32_t *nranks, int32_t *nccl_version);
+void qg_comm_destroy(qgComm *comm);
+/* Renderer_MPI::Render (:123-207) up to the resolve: this rank's shard of `params` into d_accum / d_depth (device, zeroed by
+ * the caller, as for qg_render_accumulate), then the reduce to rank 0 on the same stream; returns when both have finished.
+ * Rank 0 then calls qg_resolve. stats = this rank's. */
+int qg_comm_render(qgScene *scene, qgComm *comm, const qgRenderParams *params, int32_t tile_split, float *d_accum, float *d_depth,
+                   void *stream, qgRenderStats *stats);
+
+/* One process, several GPUs: ncclCommInitAll over `devices` (NULL = 0..ndev-1), a scene replica, a host thread and a frame
+ * buffer per device. qg_multi_render = qg_render over all of them: host outputs as for qg_render, stats summed over the ranks
+ * (times = the slowest rank's). rank_image_prefix != NULL also writes <prefix>rank_<r>_{color,depth,sample}Buffer.png, the
+ * per-rank planes Renderer_MPI::Render saves before its gather (:132-138). */
+typedef struct qgMulti qgMulti;
+int qg_multi_create(const int32_t *devices, int32_t ndev, qgMulti **out);
+int qg_multi_load_xml(qgMulti *multi, const char *xml_path, const char *asset_dir);
+int qg_multi_create_scene(qgMulti *multi, const qgSceneDesc *desc);
+qgScene *qg_multi_scene(qgMulti *multi, int32_t rank); /* rank's replica (owned by multi) */
+int qg_multi_render(qgMulti *multi, const qgRenderParams *params, int32_t tile_split, const char *rank_image_prefix, float *rgb_mean,
+                    uint8_t *rgb8, float *depth, uint8_t *sample_count, uint8_t *mask, qgRenderStats *stats);
+void qg_multi_destroy(qgMulti *multi);
+
 /* FrameBuffer::SavePNG family (src/fb/framebuffer.cpp:62-143): colour, normalised depth, sample-count images. */
 int qg_save_png_rgb8(const char *path, const uint8_t *rgb8, int32_t width, int32_t height);
 int qg_save_png_depth(const char *path, const float *depth, int32_t width, int32_t height);
 int qg_save_png_gray8(const char *path, const uint8_t *gray, int32_t width, int32_t height);
+/* FrameBuffer::ComputeSampleCountImage + SaveSampleCountImage (framebuffer.cpp:88-107,137-140): the sample-count plane
+ * stretched to 255 * (s - smin) / (smax - smin), all zero when every pixel took the same number of samples */
+int qg_save_png_sample_count(const char *path, const uint8_t *sample_count, int32_t width, int32_t height);
 
 #ifdef __cplusplus
 }

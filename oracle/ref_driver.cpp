@@ -381,6 +381,30 @@ void qaref_render_adaptive_serial(int sppMin, int sppMax, float *rgb, float *dep
   }
 }
 
+// The same loop over the pixel rows [j0, j1) only (fixed spp): lets tools/make_image_golden.py spread a 1024-spp frame
+// over several processes (the reference's scene and RNG are process-global). rgb / depth are full-frame buffers.
+void qaref_render_linear_rows(int spp, int j0, int j1, float *rgb, float *depth)
+{
+  const int W = (int) g_renderer->W(), H = (int) g_renderer->H();
+  for (int j = std::max(0, j0); j < std::min(H, j1); ++j)
+    for (int i = 0; i < W; ++i) {
+      SuperSamplerHalton sampler(Color3f(0.005f, 0.001f, 0.005f), spp, spp);
+      float d = 0.f;
+      while (sampler.Loop()) {
+        float c[3], z;
+        qaref_sample(i, j, sampler.GetSampleID(), c, &z);
+        if (sampler.GetSampleID() == 0) d = z;
+        sampler.Accumulate(Color3f(c[0], c[1], c[2]));
+        sampler.Increment();
+      }
+      const Color3f &m = sampler.GetColor();
+      rgb[3 * (j * W + i) + 0] = m.r;
+      rgb[3 * (j * W + i) + 1] = m.g;
+      rgb[3 * (j * W + i) + 2] = m.b;
+      if (depth) depth[j * W + i] = d;
+    }
+}
+
 // The reference's real render (ThreadRender with its own scheduler): fills rgb8 / depth / sampleCount.
 // Returns elapsed seconds of ThreadRender.
 double qaref_render(uint8_t *rgb8, float *depth, uint8_t *sampleCount)
@@ -411,12 +435,12 @@ int qaref_threads(void) { return (int) tasking::get_num_of_threads(); }
 }  // extern "C"
 
 #ifdef QAREF_MAIN
-// qaref_perf <scene.xml> <asset_dir> <spp> <bounce> [threads] [out.ppm]
+// qaref_perf <scene.xml> <asset_dir> <spp> <bounce> [threads] [repeat] [rgb8_out_prefix]
 // Times the reference's own ThreadRender (its TBB/OpenMP tile loop) and prints one JSON line.
 int main(int argc, char **argv)
 {
   if (argc < 5) {
-    fprintf(stderr, "usage: %s scene.xml asset_dir spp bounce [threads] [repeat]\n", argv[0]);
+    fprintf(stderr, "usage: %s scene.xml asset_dir spp bounce [threads] [repeat] [rgb8_out_prefix]\n", argv[0]);
     return 2;
   }
   int spp = atoi(argv[3]), bounce = atoi(argv[4]);
@@ -425,8 +449,16 @@ int main(int argc, char **argv)
   qaref_set_params(spp, spp, bounce, 1, threads);
   if (!qaref_load(argv[1], argv[2], 1)) { fprintf(stderr, "load failed\n"); return 1; }
   const size_t W = g_renderer->W(), H = g_renderer->H();
+  // rgb8_out_prefix: the colour plane PixelRender wrote (renderer.cpp:348-361) of repeat r goes to <prefix><r>.rgb8
+  // (raw W*H*3 bytes), so bench.py can state the image RMSE of the GPU frame against the reference's frame
+  const char *dump = argc > 7 ? argv[7] : nullptr;
+  std::vector<uint8_t> img(dump ? W * H * 3 : 0);
   for (int r = 0; r < repeat; ++r) {
-    double dt = qaref_render(nullptr, nullptr, nullptr);
+    double dt = qaref_render(dump ? img.data() : nullptr, nullptr, nullptr);
+    if (dump) {
+      const std::string path = std::string(dump) + std::to_string(r) + ".rgb8";
+      if (FILE *fp = fopen(path.c_str(), "wb")) { fwrite(img.data(), 1, img.size(), fp); fclose(fp); }
+    }
     uint64_t c = 0, s = 0;
     qaref_counters(&c, &s, 1);
     printf("{\"scene\": \"%s\", \"width\": %zu, \"height\": %zu, \"spp\": %d, \"bounce\": %d, "

@@ -122,7 +122,21 @@ PROTOTYPES = {
     "qg_save_png_rgb8": (C.c_int, [C.c_char_p, vp, i32, i32]),
     "qg_save_png_depth": (C.c_int, [C.c_char_p, vp, i32, i32]),
     "qg_save_png_gray8": (C.c_int, [C.c_char_p, vp, i32, i32]),
+    "qg_save_png_sample_count": (C.c_int, [C.c_char_p, vp, i32, i32]),
+    "qg_shard_params": (C.c_int, [C.POINTER(RenderParams), i32, i32, i32, C.POINTER(RenderParams)]),
+    "qg_comm_unique_id": (C.c_int, [vp]),
+    "qg_comm_create": (C.c_int, [vp, C.c_int, C.c_int, C.POINTER(vp)]),
+    "qg_comm_info": (C.c_int, [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)]),
+    "qg_comm_destroy": (None, [vp]),
+    "qg_comm_render": (C.c_int, [vp, vp, C.POINTER(RenderParams), i32, vp, vp, vp, C.POINTER(RenderStats)]),
+    "qg_multi_create": (C.c_int, [C.POINTER(i32), i32, C.POINTER(vp)]),
+    "qg_multi_load_xml": (C.c_int, [vp, C.c_char_p, C.c_char_p]),
+    "qg_multi_create_scene": (C.c_int, [vp, C.POINTER(SceneDesc)]),
+    "qg_multi_scene": (vp, [vp, i32]),
+    "qg_multi_render": (C.c_int, [vp, C.POINTER(RenderParams), i32, C.c_char_p, vp, vp, vp, vp, vp, C.POINTER(RenderStats)]),
+    "qg_multi_destroy": (None, [vp]),
 }
+QG_COMM_ID_BYTES = 128
 
 _libs = {}
 

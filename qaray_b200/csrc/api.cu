@@ -23,7 +23,7 @@ using namespace qb;
 namespace {
 
 thread_local std::string g_err;
-int g_device = -1;
+int g_device = -1;  // the device qg_init chose: where scenes are created from then on (each scene remembers its own)
 
 int fail(int code, const std::string &msg)
 {
@@ -83,6 +83,7 @@ struct DevBuf {
 }  // namespace
 
 struct qgScene {
+  int device = 0;  // every entry point that takes the scene makes this the calling thread's current device
   FlatScene flat;
   DScene dev;
   DevBuf<DNode> nodes;
@@ -123,6 +124,12 @@ struct qgScene {
 };
 
 namespace {
+
+int use_scene(const qgScene *sc)
+{
+  if (cudaSetDevice(sc->device) != cudaSuccess) return fail(QG_ENODEVICE, "no CUDA device: qaray_b200 has no CPU path");
+  return QG_OK;
+}
 
 void put_texcolor_dev(const qgTexturedColor &q, DTexColor *o)
 {
@@ -877,3 +884,4 @@ int resolve_to_host(qgScene *sc, int W, int H, int spp, int srgb, const float *d
 }  // namespace
 
 #include "api_entry.inc"  // the extern "C" entry points
+#include "api_multi.inc"  // ... and the multi-GPU ones (NCCL)

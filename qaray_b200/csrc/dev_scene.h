@@ -27,7 +27,7 @@ namespace qb {
 #define QB_MIN_BLOCKS_ANY 8  // any-hit kernels keep less state: 64 registers without spills, 7 % faster than at 6 (measured)
 #endif
 #ifndef QB_STACK
-#define QB_STACK 48         // deferred far children per ray = max BVH depth supported (the reference keeps 40 entries, objects.cpp:331)
+#define QB_STACK 40         // deferred far children per ray = max BVH depth supported (the reference keeps 40 entries too, objects.cpp:331)
 #endif
 
 struct DNode {

@@ -164,6 +164,29 @@ __device__ __forceinline__ bool tri_accept(const Ray3 &r, float z, V3 A, V3 B, V
   return ok;
 }
 
+// IntersectTriangle without the comparison against the running hit distance (`hInfo.z > t`, objects.cpp:229): true when the
+// triangle would be accepted by a ray whose hInfo.z is still beyond t. Lets a warp test the triangles of several leaves
+// side by side; the owner of the ray applies `z > t` afterwards in the reference's order.
+__device__ __forceinline__ bool tri_candidate(const Ray3 &r, V3 A, V3 B, V3 C, V3 N, float s, int axis, float &t_out)
+{
+  const float dz = dot(r.d, N);
+  const float pz = dot(r.p - A, N);
+  const float t = -pz / dz;
+  bool ok = !(qabs(dz) < 1e-7f) && !(t <= QB_BIAS);
+  const V3 p = r.p + t * r.d;
+  const bool a0 = axis == 0, a2 = axis == 2;
+  const float pu = a0 ? p.y : p.x, pv = a2 ? p.y : p.z;
+  const float Au = a0 ? A.y : A.x, Av = a2 ? A.y : A.z;
+  const float Bu = a0 ? B.y : B.x, Bv = a2 ? B.y : B.z;
+  const float Cu = a0 ? C.y : C.x, Cv = a2 ? C.y : C.z;
+  const float a = ((Bu - pu) * (Cv - pv) - (Cu - pu) * (Bv - pv)) * s;
+  const float b = ((Cu - pu) * (Av - pv) - (Au - pu) * (Cv - pv)) * s;
+  const float c = 1.f - a - b;
+  ok = ok && !(a < 0 || b < 0 || c < 0);
+  t_out = t;
+  return ok;
+}
+
 // TraceBVHNode. ANY = stop at the first accepted triangle (the reference finishes the traversal, but its
 // return value is the same boolean). Returns the slot of the last accepted triangle (closest) or -1; z updated.
 template <bool ANY>

@@ -147,9 +147,12 @@ template <bool PRIMARY>
 __global__ void __launch_bounds__(QB_BLOCK, QB_MIN_BLOCKS) k_wf_trace(const DScene S, const WfBuffers B, const WfParams P)
 {
   __shared__ uint32_t s_stack[QB_STACK * QB_BLOCK];
+  __shared__ SceneTab s_tab;
+  __shared__ uint32_t s_coop[(QB_BLOCK / 32) * QB_COOP_SLOTS];
   TraceCounters cnt = {0, 0, 0};
   WfClosestIO<PRIMARY> io{B, P, PRIMARY ? P.n_paths : min(B.counters[QB_CNT_PATHS + P.depth], B.capacity)};
-  traverse_pool<false>(S, io, s_stack, cnt);
+  load_scene_tab(S, s_tab);
+  traverse_pool<false>(S, io, s_stack, s_coop, s_tab, cnt);
   flush_counters(B.stats, cnt);
 }
 
@@ -230,12 +233,15 @@ template <bool PRIMARY>
 __global__ void __launch_bounds__(QB_BLOCK, QB_MIN_BLOCKS) k_redo_exact(const DScene S, const WfBuffers B, const WfParams P)
 {
   __shared__ uint32_t s_stack[QB_STACK * QB_BLOCK];
+  __shared__ SceneTab s_tab;
+  __shared__ uint32_t s_coop[(QB_BLOCK / 32) * QB_COOP_SLOTS];
   const uint32_t n = min(B.counters[QB_CNT_REDO + P.depth], B.redo_capacity);
   if (n == 0u) return;
   TraceCounters cnt = {0, 0, 0};
   WfClosestIO<PRIMARY> base{B, P, 0u};
   RedoIO<WfClosestIO<PRIMARY>> io{base, wf_redo_queue(B, P), n};
-  traverse_pool<false>(S, io, s_stack, cnt);
+  load_scene_tab(S, s_tab);
+  traverse_pool<false>(S, io, s_stack, s_coop, s_tab, cnt);
   flush_counters(B.stats, cnt);
 }
 
@@ -287,9 +293,12 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_finish(const DScene S, const Wf
 __global__ void __launch_bounds__(QB_BLOCK, QB_MIN_BLOCKS_ANY) k_wf_shadow(const DScene S, const WfBuffers B, const WfParams P)
 {
   __shared__ uint32_t s_stack[QB_STACK * QB_BLOCK];
+  __shared__ SceneTab s_tab;
+  __shared__ uint32_t s_coop[(QB_BLOCK / 32) * QB_COOP_SLOTS];
   TraceCounters cnt = {0, 0, 0};
   WfShadowIO io{B, P, min(B.counters[QB_CNT_SHADOW + P.depth], B.shadow_capacity)};
-  traverse_pool<true>(S, io, s_stack, cnt);
+  load_scene_tab(S, s_tab);
+  traverse_pool<true>(S, io, s_stack, s_coop, s_tab, cnt);
   flush_counters(B.stats, cnt, 5);
 }
 
@@ -332,9 +341,12 @@ struct WfAreaIO {
 __global__ void __launch_bounds__(QB_BLOCK, QB_MIN_BLOCKS_ANY) k_wf_area_shadow(const DScene S, const WfBuffers B, const WfParams P)
 {
   __shared__ uint32_t s_stack[QB_STACK * QB_BLOCK];
+  __shared__ SceneTab s_tab;
+  __shared__ uint32_t s_coop[(QB_BLOCK / 32) * QB_COOP_SLOTS];
   TraceCounters cnt = {0, 0, 0};
   WfAreaIO io{S, B, P, min(B.counters[QB_CNT_AREA + P.depth], B.area_capacity) * (uint32_t) QB_AREA_SPP_MAX};
-  traverse_pool<true>(S, io, s_stack, cnt);
+  load_scene_tab(S, s_tab);
+  traverse_pool<true>(S, io, s_stack, s_coop, s_tab, cnt);
   flush_counters(B.stats, cnt, 5);
 }
 
@@ -430,8 +442,11 @@ struct RayBufAnyIO {
 __global__ void __launch_bounds__(QB_BLOCK) k_trace_closest_rays(const DScene S, RayBufClosestIO io, unsigned long long *stats)
 {
   __shared__ uint32_t s_stack[QB_STACK * QB_BLOCK];
+  __shared__ SceneTab s_tab;
+  __shared__ uint32_t s_coop[(QB_BLOCK / 32) * QB_COOP_SLOTS];
   TraceCounters cnt = {0, 0, 0};
-  traverse_pool<false>(S, io, s_stack, cnt);
+  load_scene_tab(S, s_tab);
+  traverse_pool<false>(S, io, s_stack, s_coop, s_tab, cnt);
   flush_counters(stats, cnt);
 }
 
@@ -471,8 +486,11 @@ __global__ void __launch_bounds__(QB_BLOCK) k_finish_rays(const DScene S, const 
 __global__ void __launch_bounds__(QB_BLOCK) k_trace_any_rays(const DScene S, RayBufAnyIO io, unsigned long long *stats)
 {
   __shared__ uint32_t s_stack[QB_STACK * QB_BLOCK];
+  __shared__ SceneTab s_tab;
+  __shared__ uint32_t s_coop[(QB_BLOCK / 32) * QB_COOP_SLOTS];
   TraceCounters cnt = {0, 0, 0};
-  traverse_pool<true>(S, io, s_stack, cnt);
+  load_scene_tab(S, s_tab);
+  traverse_pool<true>(S, io, s_stack, s_coop, s_tab, cnt);
   flush_counters(stats, cnt, 5);
 }
 
@@ -550,11 +568,14 @@ __global__ void __launch_bounds__(QB_BLOCK) k_redo_detect_rays(const DScene S, R
 __global__ void __launch_bounds__(QB_BLOCK, QB_MIN_BLOCKS) k_redo_exact_rays(const DScene S, RayBufClosestIO base, unsigned long long *stats)
 {
   __shared__ uint32_t s_stack[QB_STACK * QB_BLOCK];
+  __shared__ SceneTab s_tab;
+  __shared__ uint32_t s_coop[(QB_BLOCK / 32) * QB_COOP_SLOTS];
   const uint32_t n = min(*base.Q.count, base.Q.cap);
   if (n == 0u) return;
   TraceCounters cnt = {0, 0, 0};
   RedoIO<RayBufClosestIO> io{base, base.Q, n};
-  traverse_pool<false>(S, io, s_stack, cnt);
+  load_scene_tab(S, s_tab);
+  traverse_pool<false>(S, io, s_stack, s_coop, s_tab, cnt);
   flush_counters(stats, cnt);
 }
 // scratch: a 16-byte header (work cursor, cull-check count, cull-check cursor), two float4 records per ray, then the

@@ -17,6 +17,19 @@
 
 namespace qb {
 
+#ifndef QB_COOP_LEAF
+#define QB_COOP_LEAF 1
+#endif
+#ifndef QB_W_LEAF
+#define QB_W_LEAF 8
+#endif
+#ifndef QB_W_NEXT
+#define QB_W_NEXT 6
+#endif
+#ifndef QB_W_FETCH
+#define QB_W_FETCH 4
+#endif
+#define QB_COOP_SLOTS 128          // (ray, triangle) pairs a warp's LEAF phase handles per round
 #define QB_REF_EMPTY 0x7FFFFFFFu   // "no current node" (an internal index never reaches 2^31-1)
 #ifndef QB_INNER_REPS
 #define QB_INNER_REPS 3            // node visits per vote while the inner group holds together
@@ -31,6 +44,119 @@ struct HitRec {
   int last_tri;         // last accepted triangle of any mesh (stale mtlID)
 };
 
+// ---- per-block scene table ------------------------------------------------------------------------------------------
+// Setting up the next object of a ray (NEXT phase) used to chase five dependent global loads (obj_node -> nodes ->
+// chain_off -> chain -> node matrix -> mesh record) at 12-14 of 32 lanes: a quarter of the kernel's instructions and
+// most of its long-scoreboard stalls per ray. The object list is tiny (tower 6, xmas 15 objects), so every block keeps
+// it in shared memory: the ToNodeCoords matrices of the first QB_TAB_NODES scene nodes, and one 48-byte record per object
+// (mesh box, root ref, the cull's sanity distance, type, ancestor chain). Scenes larger than the table read the rest
+// from global memory through the same accessors.
+#ifndef QB_TAB_NODES
+#define QB_TAB_NODES 24
+#endif
+#ifndef QB_TAB_OBJS
+#define QB_TAB_OBJS 24
+#endif
+#define QB_TAB_CHAIN 64
+#define QB_NO_FACES 0x7FFFFFFEu  // root_ref of a mesh without triangles (TriObj::IntersectRay never reaches the BVH)
+
+struct ObjRec {
+  float4 lo;  // mesh bmin.xyz, root_ref (uint bits)
+  float4 hi;  // mesh bmax.xyz, 1000 * length(bmax - bmin)
+  int4 id;    // type, -, chain begin, chain end (into the chain list: ancestors root-first, root excluded, object node last)
+};
+
+struct SceneTab {
+  float4 node[QB_TAB_NODES][3];  // i0, i1, i2 of DNode
+  ObjRec obj[QB_TAB_OBJS];
+  int chain[QB_TAB_CHAIN];
+  int chain_ok;                  // every chain entry of the first QB_TAB_OBJS objects is in chain[]
+};
+
+__device__ __forceinline__ ObjRec make_obj_rec(const DScene &S, int k)
+{
+  ObjRec o;
+  const DNode *nd = &S.nodes[__ldg(&S.obj_node[k])];
+  const int type = __ldg(&nd->type);
+  o.id = make_int4(type, 0, __ldg(&S.chain_off[k]), __ldg(&S.chain_off[k + 1]));
+  o.lo = make_float4(0.f, 0.f, 0.f, __uint_as_float(QB_NO_FACES));
+  o.hi = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (type == QG_OBJ_MESH) {
+    const DMesh *m = &S.meshes[__ldg(&nd->mesh)];
+    const V3 bmin = v3(__ldg(&m->bmin[0]), __ldg(&m->bmin[1]), __ldg(&m->bmin[2]));
+    const V3 bmax = v3(__ldg(&m->bmax[0]), __ldg(&m->bmax[1]), __ldg(&m->bmax[2]));
+    const uint32_t root = __ldg(&m->num_faces) != 0u ? __ldg(&m->root_ref) : QB_NO_FACES;
+    o.lo = make_float4(bmin.x, bmin.y, bmin.z, __uint_as_float(root));
+    o.hi = make_float4(bmax.x, bmax.y, bmax.z, 1000.f * length(bmax - bmin));
+  }
+  return o;
+}
+
+// all threads of the block; ends with __syncthreads()
+__device__ __forceinline__ void load_scene_tab(const DScene &S, SceneTab &T)
+{
+  for (int i = threadIdx.x; i < min(S.num_nodes, QB_TAB_NODES); i += blockDim.x) {
+    T.node[i][0] = __ldg(&S.nodes[i].i0);
+    T.node[i][1] = __ldg(&S.nodes[i].i1);
+    T.node[i][2] = __ldg(&S.nodes[i].i2);
+  }
+  const int no = min(S.num_obj, QB_TAB_OBJS);
+  for (int k = threadIdx.x; k < no; k += blockDim.x) T.obj[k] = make_obj_rec(S, k);
+  const int nc = __ldg(&S.chain_off[no]);
+  for (int c = threadIdx.x; c < min(nc, QB_TAB_CHAIN); c += blockDim.x) T.chain[c] = __ldg(&S.chain[c]);
+  if (threadIdx.x == 0) T.chain_ok = nc <= QB_TAB_CHAIN;
+  __syncthreads();
+}
+
+__device__ __forceinline__ Ray3 to_node_q(float4 i0, float4 i1, float4 i2, Ray3 r)  // to_node on loaded matrix rows
+{
+  const V3 pos = v3(i0.w, i1.w, i2.w);
+  const V3 a = r.p - pos;
+  const V3 b = (r.p + r.d) - pos;
+  Ray3 o;
+  o.p = v3(i0.x * a.x + i1.x * a.y + i2.x * a.z, i0.y * a.x + i1.y * a.y + i2.y * a.z, i0.z * a.x + i1.z * a.y + i2.z * a.z);
+  const V3 q = v3(i0.x * b.x + i1.x * b.y + i2.x * b.z, i0.y * b.x + i1.y * b.y + i2.y * b.z, i0.z * b.x + i1.z * b.y + i2.z * b.z);
+  o.d = q - o.p;
+  return o;
+}
+__device__ __forceinline__ Ray3 to_node_tab(const DScene &S, const SceneTab &T, int n, Ray3 r)
+{
+  if (n < QB_TAB_NODES) return to_node_q(T.node[n][0], T.node[n][1], T.node[n][2], r);
+  return to_node(&S.nodes[n], r);
+}
+__device__ __forceinline__ ObjRec obj_rec(const DScene &S, const SceneTab &T, int k)
+{
+  if (k < QB_TAB_OBJS) return T.obj[k];
+  return make_obj_rec(S, k);
+}
+// ray of object k's node space (the root's transform already applied to r0): chain_ray through the table
+__device__ __forceinline__ Ray3 chain_ray_tab(const DScene &S, const SceneTab &T, const ObjRec &o, int k, Ray3 r0)
+{
+  Ray3 r = r0;
+  if (k < QB_TAB_OBJS && T.chain_ok) {
+    for (int c = o.id.z; c < o.id.w; ++c) r = to_node_tab(S, T, T.chain[c], r);
+  } else {
+    for (int c = o.id.z; c < o.id.w; ++c) r = to_node_tab(S, T, __ldg(&S.chain[c]), r);
+  }
+  return r;
+}
+// Box::IntersectRay of mesh_box_hit on the table's box
+__device__ __forceinline__ bool mesh_box_hit_q(const ObjRec &o, const Ray3 &r, float t_max, float &exit_out, V3 &drcp)
+{
+  drcp = v3(1.f, 1.f, 1.f) / r.d;
+  const V3 bmin = v3(o.lo.x, o.lo.y, o.lo.z), bmax = v3(o.hi.x, o.hi.y, o.hi.z);
+  const V3 p0 = -(r.p - bmin) * drcp;
+  const V3 p1 = -(r.p - bmax) * drcp;
+  float t0x, t1x, t0y, t1y, t0z, t1z;
+  if (qabs(r.d.x) < 1e-7f) { t0x = -QB_BIGFLOAT; t1x = QB_BIGFLOAT; } else { t0x = qmin(p0.x, p1.x); t1x = qmax(p0.x, p1.x); }
+  if (qabs(r.d.y) < 1e-7f) { t0y = -QB_BIGFLOAT; t1y = QB_BIGFLOAT; } else { t0y = qmin(p0.y, p1.y); t1y = qmax(p0.y, p1.y); }
+  if (qabs(r.d.z) < 1e-7f) { t0z = -QB_BIGFLOAT; t1z = QB_BIGFLOAT; } else { t0z = qmin(p0.z, p1.z); t1z = qmax(p0.z, p1.z); }
+  const float entry = qmax(t0x, qmax(t0y, t0z));
+  const float exit = qmin(t1x, qmin(t1y, t1z));
+  exit_out = exit;
+  return !(entry > t_max || entry > exit);
+}
+
 // IO concept:
 //   uint32_t count() const                       number of rays
 //   uint32_t *cursor()                           device work cursor
@@ -38,12 +164,12 @@ struct HitRec {
 //   void store(uint32_t idx, const HitRec &)     closest
 //   void store_any(uint32_t idx, bool occluded)  any-hit
 template <bool ANY, class IO>
-__device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t *__restrict__ s_stack, TraceCounters &cnt)
+__device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t *__restrict__ s_stack, uint32_t *__restrict__ s_coop,
+                                              const SceneTab &T, TraceCounters &cnt)
 {
   const int lane = threadIdx.x & 31;
   const uint32_t lt_mask = (1u << lane) - 1u;
   const uint32_t n = io.count();
-  const DNode *root = &S.nodes[0];
   uint32_t *stk = s_stack + threadIdx.x;  // entry e at stk[e * QB_BLOCK]
 
   bool active = false, exhausted = false;
@@ -77,7 +203,9 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
     if ((m_fetch | m_inner | m_leaf | m_next) == 0u) break;
     const int n_fetch = __popc(m_fetch), n_inner = __popc(m_inner), n_leaf = __popc(m_leaf), n_next = __popc(m_next);
 
-    if (n_inner >= n_leaf && n_inner >= n_next && n_inner >= n_fetch) {
+    // weighted plurality (weights in quarters): the cheap phases may be given more than their head count
+    const int w_inner = 4 * n_inner, w_leaf = QB_W_LEAF * n_leaf, w_next = QB_W_NEXT * n_next, w_fetch = QB_W_FETCH * n_fetch;
+    if (w_inner >= w_leaf && w_inner >= w_next && w_inner >= w_fetch) {
       // ---- INNER: node visits (both children's boxes); the near child becomes current, the far child is deferred.
       // Up to QB_INNER_REPS visits per vote while at least half of the lanes that started are still on inner nodes.
 #pragma unroll 1
@@ -173,9 +301,15 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
           }
         }
       }
-    } else if (n_leaf >= n_next && n_leaf >= n_fetch) {
-      // ---- LEAF: the leaf's triangles in elements[] order, branch-free per triangle ------------------------------------
-      if (s_leaf) {
+    } else if (w_leaf >= w_next && w_leaf >= w_fetch) {
+      // ---- LEAF: the leaves' triangles, pooled over the warp -------------------------------------------------------------
+      // A lane looping over its own leaf's 1..8 triangles kept the other lanes of the phase waiting for the longest leaf
+      // (9 of 32 threads per instruction in the round-1 capture). The (ray, triangle) pairs of all leaf lanes are laid out
+      // in one list instead and every lane of the warp tests one pair per pass — everything of IntersectTriangle that does
+      // not depend on the running hit distance — with the owner's ray fetched by shuffle; the owner then applies
+      // `hInfo.z > t` to its results in elements[] order, so the accepted triangle and t are what the serial loop gives.
+#if !QB_COOP_LEAF
+      if (s_leaf) {  // A/B: the round-1 per-lane loop
         const uint32_t base = cur & 0x0FFFFFFFu;
         const uint32_t count = ((cur >> 28) & 7u) + 1u;
         cur = sp > 0 ? stk[(--sp) * QB_BLOCK] : QB_REF_EMPTY;
@@ -192,7 +326,59 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
           }
         }
       }
-    } else if (n_next >= n_fetch) {
+#else
+      {
+        const uint32_t lbase = cur & 0x0FFFFFFFu;
+        uint32_t count = s_leaf ? ((cur >> 28) & 7u) + 1u : 0u;
+        uint32_t incl = count;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const uint32_t v = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+          if (lane >= o) incl += v;
+        }
+        if (incl > QB_COOP_SLOTS) count = 0u;  // does not fit this round: the lane keeps its leaf for the next LEAF phase
+        const uint32_t excl = incl - count;
+        const uint32_t total = min(__reduce_max_sync(0xFFFFFFFFu, count ? incl : 0u), (uint32_t) QB_COOP_SLOTS);
+        uint32_t *scr = s_coop + (threadIdx.x >> 5) * QB_COOP_SLOTS;
+        for (uint32_t i = 0; i < count; ++i) scr[excl + i] = ((uint32_t) lane << 3) | i;
+        __syncwarp();
+        for (uint32_t q0 = 0; q0 < total; q0 += 32u) {
+          const uint32_t q = q0 + (uint32_t) lane;
+          const bool have = q < total;
+          const uint32_t code = have ? scr[q] : 0u;
+          const int o = (int) (code >> 3);
+          const uint32_t tb = __shfl_sync(0xFFFFFFFFu, lbase, o);
+          Ray3 rr;
+          rr.p.x = __shfl_sync(0xFFFFFFFFu, r.p.x, o); rr.p.y = __shfl_sync(0xFFFFFFFFu, r.p.y, o); rr.p.z = __shfl_sync(0xFFFFFFFFu, r.p.z, o);
+          rr.d.x = __shfl_sync(0xFFFFFFFFu, r.d.x, o); rr.d.y = __shfl_sync(0xFFFFFFFFu, r.d.y, o); rr.d.z = __shfl_sync(0xFFFFFFFFu, r.d.z, o);
+          if (have) {
+            const DTri *tp = &S.tris[tb + (code & 7u)];
+            const float4 ta = __ldg(&tp->a), tb4 = __ldg(&tp->b), tc = __ldg(&tp->c), td = __ldg(&tp->d);
+            QB_CNT(tris);
+            float t;
+            const bool ok = tri_candidate(rr, xyz(ta), xyz(tb4), xyz(tc), v3(ta.w, tb4.w, tc.w), td.x, __float_as_int(td.y), t);
+            // accepted candidates have t > bias > 0; bit 0 of a rejected entry's word is never looked at
+            scr[q] = ok ? __float_as_uint(t) : 0x80000000u;
+          }
+        }
+        __syncwarp();
+        if (count) {
+          cur = sp > 0 ? stk[(--sp) * QB_BLOCK] : QB_REF_EMPTY;
+          for (uint32_t i = 0; i < count; ++i) {
+            const uint32_t w = scr[excl + i];
+            const float t = __uint_as_float(w);
+            if (!(w & 0x80000000u) && h.z > t) {
+              if (ANY) { io.store_any(idx, true); active = false; break; }
+              h.z = t;
+              obj_slot = (int) (lbase + i);
+              if (__ldg(&S.tri_face[lbase + i]) & 0x80000000u) { uv_slot = obj_slot; uv_t = t; }
+            }
+          }
+        }
+        __syncwarp();  // the scratch is rewritten by the next LEAF phase
+      }
+#endif
+    } else if (w_next >= w_fetch) {
       // ---- NEXT: the object just traversed reports its result, then the next object of the list is set up ----------
       bool redo = false;
       if (s_next && k > 0 && cull_state == 1) {
@@ -205,7 +391,7 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
           cull_state = 2;
           h.z = z_entry;
           obj_slot = -1; uv_slot = -1; sp = 0;
-          cur = __ldg(&S.meshes[__ldg(&S.nodes[__ldg(&S.obj_node[k - 1])].mesh)].root_ref);
+          cur = __float_as_uint(obj_rec(S, T, k - 1).lo.w);
         }
       }
       if (s_next && !redo) {
@@ -218,23 +404,19 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
           if (ANY) io.store_any(idx, false); else io.store(idx, h);
           active = false;
         } else {
-          const DNode *nd = &S.nodes[__ldg(&S.obj_node[k])];
-          r = chain_ray(S, k, c0);
-          const int type = __ldg(&nd->type);
+          const ObjRec o = obj_rec(S, T, k);
+          r = chain_ray_tab(S, T, o, k, c0);
+          const int type = o.id.x;
           QB_CNT(objects);
           ++k;
           obj_slot = -1; uv_slot = -1;
           if (type == QG_OBJ_MESH) {
-            const DMesh *m = &S.meshes[__ldg(&nd->mesh)];
-            if (__ldg(&m->num_faces) != 0u && mesh_box_hit(m, r, h.z, mesh_exit, drcp)) {
-              cur = __ldg(&m->root_ref);
+            const uint32_t root_ref = __float_as_uint(o.lo.w);
+            if (root_ref != QB_NO_FACES && mesh_box_hit_q(o, r, h.z, mesh_exit, drcp)) {
+              cur = root_ref;
               cull_state = io.exact(idx, k - 1) ? 2 : 0;  // k was advanced above: k - 1 is this object
               z_entry = h.z;
-              {
-                const V3 ext = v3(__ldg(&m->bmax[0]) - __ldg(&m->bmin[0]), __ldg(&m->bmax[1]) - __ldg(&m->bmin[1]),
-                                  __ldg(&m->bmax[2]) - __ldg(&m->bmin[2]));
-                z_sane = qmax(mesh_exit * 1.001f, 1000.f * length(ext));
-              }
+              z_sane = qmax(mesh_exit * 1.001f, o.hi.w);
               gx = qabs(r.d.x) < 1e-7f; gy = qabs(r.d.y) < 1e-7f; gz = qabs(r.d.z) < 1e-7f;
             }
           } else {
@@ -264,7 +446,7 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
         const uint32_t ray = my < n ? io.map(my) : my;
         if (my < n && io.load(ray, c, tmax)) {
           idx = ray;
-          c0 = to_node(root, c);
+          c0 = to_node_tab(S, T, 0, c);
           h.z = tmax; h.k = -1; h.slot = -1; h.tex_k = -1; h.tex_slot = -1; h.tex_t = 0.f; h.last_tri = -1;
           k = 0; sp = 0; cur = QB_REF_EMPTY; obj_slot = -1; uv_slot = -1;
           active = true;
