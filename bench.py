@@ -51,14 +51,29 @@ def parse_args():
     ap.add_argument("--width", type=int, default=0)
     ap.add_argument("--height", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--strong-spp", type=int, default=512, help="total spp of the strong-scaling sub-record (0 = skip); the same frame at every N")
+    ap.add_argument("--tile-split", type=int, default=0, help="G_t of the strong job's G = G_t x G_s split (0 = 2 when N >= 4, else 1)")
     ap.add_argument("--sort-materials", action="store_true", help="qgRenderParams.sort_by_material = 1 (measured option, default off)")
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target length of the bounded CPU sample")
     return ap.parse_args()
 
 
-def workload(args):
-    return {"workload": "inputs/%s.xml (stand-in geometry from tools/gen_assets.py), %d spp/GPU/step, bounce %d, sRGB" % (
-        args.scene, args.spp, BOUNCE), "scene": args.scene, "spp_per_gpu": args.spp, "max_bounce": BOUNCE}
+def workload(args, width, height, world):
+    """the `config` object: the same keys and values on the b200 arm and the reference arm (the driver compares them)"""
+    return {"workload": "inputs/%s.xml (stand-in geometry from tools/gen_assets.py), %dx%d, %d spp/GPU/step, bounce %d, sRGB" % (
+        args.scene, width, height, args.spp, BOUNCE), "scene": args.scene, "width": width, "height": height,
+            "spp_per_gpu": args.spp, "spp_total": args.spp * world, "max_bounce": BOUNCE,
+            "parallelism": "sample-shard x%d + NCCL reduce" % world if world > 1 else "1 GPU",
+            "l2": "256 MiB device memset between steps (inside the timed region, ~0.1 ms); path-state working set also exceeds L2"}
+
+
+def host_threads():
+    """every host core this process may use. torch.distributed.run exports OMP_NUM_THREADS=1 to its workers: the reference arm
+    must not inherit that (round-1 verdict: a 1-thread reference at N >= 2), so the count is passed to qaref_perf explicitly."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
 
 
 # ------------------------------------------------------------------------------------------------- clocks
@@ -130,28 +145,38 @@ def ref_rays_per_sample(scene, spp=2):
     raise RuntimeError("reference ray counting failed: %s" % out[-500:])
 
 
-def ref_perf_run(scene, spp, repeat, threads=0):
-    """the reference's own ThreadRender (its OpenMP tile loop, -O2 -march build) -> seconds per repeat"""
+def ref_perf_run(scene, spp, repeat, threads=None, dump_prefix=None):
+    """the reference's own ThreadRender (its OpenMP tile loop, -O2 -march build) -> seconds per repeat, on ALL host cores;
+    dump_prefix: repeat r's colour plane (rgb8) goes to <prefix><r>.rgb8"""
+    threads = threads or host_threads()
     cmd = [REF_PERF, os.path.join(REF_INPUTS, scene + ".xml"), ASSETS, str(spp), str(BOUNCE), str(threads), str(repeat)]
-    out = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, timeout=3600).stdout
+    if dump_prefix:
+        cmd.append(dump_prefix)
+    env = dict(os.environ, OMP_NUM_THREADS=str(threads))
+    env.pop("OMP_PROC_BIND", None)
+    out = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, timeout=3600, env=env).stdout
     recs = [json.loads(l) for l in out.splitlines() if l.startswith("{")]
     if len(recs) != repeat:
         raise RuntimeError("qaref_perf failed: %s" % out[-500:])
     return recs
 
 
-def cpu_baseline(scene, target_seconds):
-    """bounded sample: calibrate at 1 spp, then one run sized for about target_seconds"""
+def cpu_baseline(scene, target_seconds, dump_prefix=None):
+    """bounded sample: calibrate at 1 spp, then two back-to-back renders (the process's RNG streams run on, so the second is
+    an independent estimate of the same frame) sized for about target_seconds together; both frames are kept for image_rmse"""
     rps, _, _ = ref_rays_per_sample(scene)
     cal = ref_perf_run(scene, 1, 1)[0]
-    spp = int(max(1, min(256, round(target_seconds / max(cal["seconds"], 1e-3)))))
-    rec = ref_perf_run(scene, spp, 1)[0]
-    mrays = rec["samples"] * rps / rec["seconds"] * 1e-6
-    return {"value": mrays, "unit": METRIC, "cores": rec["threads"], "kind": "reference",
-            "sample": "%s at %dx%d, %d spp, bounce %d: %.2f s on %d OpenMP threads (reference's own ThreadRender, "
+    spp = int(max(1, min(256, round(0.5 * target_seconds / max(cal["seconds"], 1e-3)))))
+    recs = ref_perf_run(scene, spp, 2, dump_prefix=dump_prefix)
+    secs = sum(r["seconds"] for r in recs)
+    samples = sum(r["samples"] for r in recs)
+    mrays = samples * rps / secs * 1e-6
+    rec = recs[0]
+    return {"value": mrays, "unit": METRIC, "cores": rec["threads"], "host_cores": host_threads(), "kind": "reference",
+            "sample": "%s at %dx%d, 2 x %d spp, bounce %d: %.2f s on %d OpenMP threads (reference's own ThreadRender, "
                       "oracle/_ref/qaref_perf); %.3f rays/sample counted by the reference" % (
-                          scene, rec["width"], rec["height"], spp, BOUNCE, rec["seconds"], rec["threads"], rps),
-            "samples_per_s": rec["samples"] / rec["seconds"], "rays_per_sample": rps}
+                          scene, rec["width"], rec["height"], spp, BOUNCE, secs, rec["threads"], rps),
+            "samples_per_s": samples / secs, "rays_per_sample": rps, "spp": spp, "width": rec["width"], "height": rec["height"]}
 
 
 def run_reference_arm(args):
@@ -169,13 +194,13 @@ def run_reference_arm(args):
     secs = sum(r["seconds"] for r in recs)
     samples = sum(r["samples"] for r in recs)
     val = samples * rps / secs * 1e-6
-    cfg = workload(args)
-    cfg["reference_sample_spp"] = spp
+    cfg = workload(args, args.width or cal["width"], args.height or cal["height"], max(1, args.gpus))
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": METRIC, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": secs / len(recs) * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
             "samples_per_s": samples / secs,
-            "cpu_baseline": {"value": val, "unit": METRIC, "cores": recs[0]["threads"], "kind": "reference",
+            "reference_sample_spp": spp,
+            "cpu_baseline": {"value": val, "unit": METRIC, "cores": recs[0]["threads"], "host_cores": host_threads(), "kind": "reference",
                              "sample": "%d spp per step (bounded sample of the %d spp workload), %.3f rays/sample" % (spp, args.spp, rps)},
             "e2e": {"value": val, "unit": METRIC, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line))
@@ -205,10 +230,24 @@ def run_b200_arm(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        os.environ.pop("NCCL_DEBUG", None)  # any level >= VERSION prints a banner on stdout; stdout carries the one JSON line
+        # NCCL_DEBUG stays as the operator set it (the rank count / transport lines are evidence); NCCL writes its log to
+        # stdout by default, which carries the one JSON line, so the log goes to stderr unless a file was asked for
+        if os.environ.get("NCCL_DEBUG") and not os.environ.get("NCCL_DEBUG_FILE"):
+            os.environ["NCCL_DEBUG_FILE"] = "/dev/stderr"
         dist.init_process_group("nccl", device_id=dev)
     lib = capi.load()
     capi.check(lib, lib.qg_init(local))
+    comm = C.c_void_p()
+    if world > 1:
+        # the library's own communicator (qgComm over NCCL): torch.distributed only ships the 128-byte unique id and keeps the
+        # harness's barriers / max-over-ranks; the timed shard render + reduce is qg_comm_render
+        uid = torch.zeros(capi.QG_COMM_ID_BYTES, dtype=torch.uint8)
+        if rank == 0:
+            capi.check(lib, lib.qg_comm_unique_id(C.c_void_p(uid.data_ptr())))
+        uid_d = uid.to(dev)
+        dist.broadcast(uid_d, 0)
+        uid = uid_d.cpu()
+        capi.check(lib, lib.qg_comm_create(C.c_void_p(uid.data_ptr()), rank, world, C.byref(comm)))
     xml = os.path.join(REF_INPUTS, args.scene + ".xml")
     t_load = time.time()
     h = C.c_void_p()
@@ -233,6 +272,7 @@ def run_b200_arm(args):
     torch.cuda.set_stream(stream)
     sptr = C.c_void_p(stream.cuda_stream)
     my = params(rank * args.spp, (rank + 1) * args.spp)
+    whole = params(0, 0)  # the whole N*S-spp frame: qg_comm_render derives this rank's shard itself (sample split, tile_split 1)
     # host output planes (pinned) for the e2e path
     pin = lambda *shape, dt=torch.uint8: torch.empty(*shape, dtype=dt).pin_memory()
     h_mean, h_rgb8, h_depth = pin(npix * 3, dt=torch.float32), pin(npix * 3), pin(npix, dt=torch.float32)
@@ -242,18 +282,22 @@ def run_b200_arm(args):
     st = capi.RenderStats()
     tot = {"closest": 0, "shadow": 0, "samples": 0, "launches": 0, "trace_ms": 0.0, "shade_ms": 0.0, "shadow_ms": 0.0, "device_ms": 0.0}
 
+    job = {"whole": whole, "tile_split": 1}  # what a step renders: the frame description all ranks share, and G_t
+
     def step(e2e, count):
         flush.zero_()  # L2 flush between steps
+        my, whole, tile_split = job["whole"], job["whole"], job["tile_split"]
         if e2e and world == 1:
             capi.check(lib, lib.qg_render(h, C.byref(my), hp(h_mean), hp(h_rgb8), hp(h_depth), hp(h_sc), hp(h_mask), C.byref(st)))
         else:
             accum.zero_()
             depth.zero_()
-            capi.check(lib, lib.qg_render_accumulate(h, C.byref(my), C.c_void_p(accum.data_ptr()), C.c_void_p(depth.data_ptr()), sptr,
-                                                     C.byref(st)))
-            if world > 1:
-                dist.reduce(accum, 0)
-                dist.reduce(depth, 0)  # only the shard owning sample 0 wrote depth: sum with zeros
+            if world > 1:  # this rank's shard + ncclReduce(sum) of both planes to rank 0, inside the library
+                capi.check(lib, lib.qg_comm_render(h, comm, C.byref(whole), tile_split, C.c_void_p(accum.data_ptr()), C.c_void_p(depth.data_ptr()), sptr,
+                                                   C.byref(st)))
+            else:
+                capi.check(lib, lib.qg_render_accumulate(h, C.byref(my), C.c_void_p(accum.data_ptr()), C.c_void_p(depth.data_ptr()), sptr,
+                                                         C.byref(st)))
             if e2e and rank == 0:
                 capi.check(lib, lib.qg_resolve(h, C.byref(my), C.c_void_p(accum.data_ptr()), C.c_void_p(depth.data_ptr()), hp(h_mean),
                                                hp(h_rgb8), hp(h_depth), hp(h_sc), hp(h_mask), sptr))
@@ -299,7 +343,58 @@ def run_b200_arm(args):
     dev_run = timed(False, args.steps, True)
     step(True, False)
     e2e_run = timed(True, args.steps, False)
+    # Strong scaling beside the weak line (the reference's MPI mode splits ONE frame over its ranks, renderer.cpp:383-398):
+    # a fixed --strong-spp frame split tile x sample over the N ranks, G = G_t x G_s, device-timed like `value`.
+    strong = None
+    if args.strong_spp > 0 and args.strong_spp % world == 0:
+        gt = args.tile_split if args.tile_split > 0 else (2 if world % 2 == 0 and world >= 4 else 1)
+        job = {"whole": params(0, 0, spp=args.strong_spp), "tile_split": gt}
+        step(False, False)
+        sr = timed(False, max(1, min(args.steps, 3)), False)
+        ns = max(1, min(args.steps, 3))
+        strong = {"scaling": "strong", "spp_total": args.strong_spp, "split": "tiles x%d (interleaved 4x4 tiles) x samples x%d" % (gt, world // gt),
+                  "steps": ns, "ms_per_step": sr["ms"] / ns, "value": sr["rays"] / (sr["ms"] * 1e-3) * 1e-6, "unit": METRIC,
+                  "rays_per_step": sr["rays"] / ns, "n_gpus": world}
+        job = {"whole": whole, "tile_split": 1}
+        step(True, False)  # leave the weak job's reduced frame in accum for the image check below
+    image_check = None
+    if world > 1:
+        # the reduced N x S-spp frame of the last step against the same frame rendered whole on rank 0's GPU (the RNG is keyed
+        # by (pixel, sample), so only the order of the fp32 additions differs). Outside the timed region.
+        red = accum.clone()
+        if rank == 0:
+            accum.zero_()
+            depth.zero_()
+            capi.check(lib, lib.qg_render_accumulate(h, C.byref(whole), C.c_void_p(accum.data_ptr()), C.c_void_p(depth.data_ptr()), sptr, None))
+            torch.cuda.synchronize()
+            a, b = red.view(-1, 4)[:, :3].double() / spp_total, accum.view(-1, 4)[:, :3].double() / spp_total
+            image_check = {"what": "NCCL-reduced %d-GPU frame vs the same %d-spp frame rendered on one GPU (linear radiance means)" % (world, spp_total),
+                           "max_abs": float((a - b).abs().max()), "rmse": float(((a - b) ** 2).mean().sqrt()),
+                           "max_rel": float(((a - b).abs() / (b.abs() + 1e-3)).max()), "mean": float(b.mean()),
+                           "weights_equal": bool(torch.equal(red.view(-1, 4)[:, 3], accum.view(-1, 4)[:, 3]))}
+        dist.barrier()
     return finish_b200(args, locals())
+
+
+def image_rmse(lib, h, L, spp, prefix):
+    """BASELINE.json `metric`: image RMSE. The GPU frame at the spp of the CPU baseline's bounded sample against the
+    reference's frame of the same workload (the rgb8 plane PixelRender writes, renderer.cpp:348-361), beside the RMSE of
+    the reference's two independent frames — the Monte-Carlo noise floor at that spp. Outside every timed region."""
+    import numpy as np
+    from qaray_b200 import capi
+    W, H = L["W"], L["H"]
+    a = np.fromfile(prefix + "0.rgb8", dtype=np.uint8).astype(np.float64) / 255.0
+    b = np.fromfile(prefix + "1.rgb8", dtype=np.uint8).astype(np.float64) / 255.0
+    g8 = np.zeros(W * H * 3, dtype=np.uint8)
+    rp = capi.RenderParams(spp, BOUNCE, 1, 0x5EED, W, H, 0, 1, 0, 0, 0, 0)
+    capi.check(lib, lib.qg_render(h, C.byref(rp), None, g8.ctypes.data_as(C.c_void_p), None, None, None, None))
+    g = g8.astype(np.float64) / 255.0
+    rm = lambda x, y: float(np.sqrt(np.mean((x - y) ** 2)))
+    return {"gpu_vs_ref": rm(g, a), "gpu_vs_ref_b": rm(g, b), "ref_vs_ref": rm(a, b), "spp": spp, "width": W, "height": H,
+            "space": "rgb8 plane / 255 (sRGB, clamped, as the reference saves it)",
+            "mean_gpu": [float(v) for v in g.reshape(-1, 3).mean(axis=0)], "mean_ref": [float(v) for v in a.reshape(-1, 3).mean(axis=0)],
+            "note": "independent Monte-Carlo estimates of one frame: gpu_vs_ref ~ ref_vs_ref means the GPU frame is as close "
+                    "to the reference's as the reference is to itself"}
 
 
 def finish_b200(args, L):
@@ -358,11 +453,9 @@ def finish_b200(args, L):
                                           "shadow": t["shadow_ms"] / args.steps, "render_total": t["device_ms"] / args.steps}}
         value = dev_run["rays"] / (dev_run["ms"] * 1e-3) * 1e-6
         e2e_v = e2e_run["rays"] / (e2e_run["ms"] * 1e-3) * 1e-6
-        cfg = workload(args)
-        cfg.update({"width": L["W"], "height": L["H"], "spp_total": L["spp_total"], "parallelism": "sample-shard x%d + NCCL reduce" % world if world > 1 else "1 GPU",
-                    "l2": "256 MiB device memset between steps (inside the timed region, ~0.1 ms); path-state working set also exceeds L2",
-                    "triangles": int(info.num_faces), "bvh_nodes": int(info.num_bvh_nodes), "scene_device_bytes": int(info.device_bytes),
-                    "scene_load_s": L["t_load"], "rays_per_sample": dev_run["rays"] / max(1.0, dev_run["samples"])})
+        cfg = workload(args, L["W"], L["H"], world)
+        scene_stats = {"triangles": int(info.num_faces), "bvh_nodes": int(info.num_bvh_nodes), "scene_device_bytes": int(info.device_bytes),
+                       "scene_load_s": L["t_load"], "rays_per_sample": dev_run["rays"] / max(1.0, dev_run["samples"])}
         out = {"metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
                "ms_per_step": dev_run["ms"] / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                "dtype": "f32", "data": "synthetic", "config": cfg,
@@ -373,15 +466,25 @@ def finish_b200(args, L):
                        "d2h_bytes_per_step": L["d2h_bytes"], "ms_per_step": e2e_run["ms"] / args.steps,
                        "note": "scene resident (uploaded once by qg_scene_load_xml, as the reference loads its scene before Render); "
                                "per-step input is the parameter block; output = rgb_mean f32 + rgb8 + depth f32 + sampleCount + mask"},
-               "roofline": roofline}
+               "roofline": roofline, "scene_stats": scene_stats}
+        if L.get("strong") is not None:
+            out["strong"] = L["strong"]
+        if L.get("image_check") is not None:
+            out["image_check"] = L["image_check"]
         if world == 1 and not args.no_cpu_baseline and ref_available():
             try:
-                out["cpu_baseline"] = cpu_baseline(args.scene, args.cpu_seconds)
+                import tempfile
+                with tempfile.TemporaryDirectory() as td:
+                    prefix = os.path.join(td, "ref_")
+                    out["cpu_baseline"] = cb = cpu_baseline(args.scene, args.cpu_seconds, prefix)
+                    if cb["width"] == L["W"] and cb["height"] == L["H"]:
+                        out["image_rmse"] = image_rmse(lib, h, L, cb["spp"], prefix)
             except Exception as e:  # the baseline is reported, never required for the GPU number
                 out["cpu_baseline"] = {"value": None, "unit": METRIC, "cores": 0, "kind": "reference", "sample": "failed: %s" % e}
         print(json.dumps(out))
     lib.qg_scene_destroy(h)
     if world > 1:
+        lib.qg_comm_destroy(L["comm"])
         dist.barrier()
         dist.destroy_process_group()
     return 0

@@ -238,6 +238,10 @@ int qg_resolve(qgScene *scene, const qgRenderParams *params, const float *d_accu
  * [sample_begin, sample_end). counts[width*height]. The kernels enumerate paths with the same code, so the shards of
  * all ranks must tile the frame exactly once per sample (tests/test_sharding.py). */
 int qg_shard_coverage(const qgCamera *camera, const qgRenderParams *params, uint16_t *counts);
+/* Host-only: the sizes the render driver derives for that shard, in 64 bits (3840 x 2160 at 1024 spp is 8.5e9 samples):
+ * pixels the shard owns, samples = pixels x its sample range (PixelRender loop iterations, renderer.cpp:310), and path
+ * slots enumerated (16 per 4x4 tile, edge tiles padded). Any output may be NULL. */
+int qg_shard_size(const qgCamera *camera, const qgRenderParams *params, uint64_t *pixels, uint64_t *samples, uint64_t *paths);
 
 /* ---- multi-GPU: the reference's rank model (Renderer_MPI, src/renderers/Renderer_MPI.cpp) over NCCL ----------------------
  * Every rank accumulates its shard of the frame — tiles k = r_t (mod G_t) of the reference's interleaved 4x4-tile rule

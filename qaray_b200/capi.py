@@ -119,6 +119,7 @@ PROTOTYPES = {
     "qg_render_accumulate": (C.c_int, [vp, C.POINTER(RenderParams), vp, vp, vp, C.POINTER(RenderStats)]),
     "qg_resolve": (C.c_int, [vp, C.POINTER(RenderParams), vp, vp, vp, vp, vp, vp, vp, vp]),
     "qg_shard_coverage": (C.c_int, [C.POINTER(Camera), C.POINTER(RenderParams), vp]),
+    "qg_shard_size": (C.c_int, [C.POINTER(Camera), C.POINTER(RenderParams), C.POINTER(u64), C.POINTER(u64), C.POINTER(u64)]),
     "qg_save_png_rgb8": (C.c_int, [C.c_char_p, vp, i32, i32]),
     "qg_save_png_depth": (C.c_int, [C.c_char_p, vp, i32, i32]),
     "qg_save_png_gray8": (C.c_int, [C.c_char_p, vp, i32, i32]),

@@ -410,9 +410,10 @@ int ensure_wf(qgScene *sc, uint32_t capacity, bool carry_diff = false)
   for (void *p : sc->wf_allocs) cudaFree(p);
   sc->wf_allocs.clear();
   sc->wf_capacity = 0;
-  // room for the dead entries of k_wf_shade's output reservations: at most one QB_OUT_CHUNK tail per shade warp and queue
+  // room for the dead entries of the shade kernels' output reservations: at most one QB_OUT_CHUNK tail per shade warp and
+  // queue, for the largest grid any material class's shade kernel may be launched with
   const uint32_t requested = capacity;
-  capacity += (uint32_t) wf_shade_grid() * (QB_BLOCK / 32) * QB_OUT_CHUNK;
+  capacity += (uint32_t) wf_shade_grid_max() * (QB_BLOCK / 32) * QB_OUT_CHUNK;
   WfBuffers &B = sc->wf;
   memset(&B, 0, sizeof B);
   auto alloc4 = [&](float4 **p, size_t n) -> cudaError_t {
@@ -492,7 +493,7 @@ bool class_carries_diff(int cls) { return cls == QG_CLASS_MONTECARLOGI || cls ==
 
 struct Shard {
   int W, H, tiles_x, tiles_y, tiles_local, s0, s1;
-  unsigned long long total_paths, valid_samples;
+  unsigned long long total_paths, valid_samples, owned_pixels;  // 64-bit: 4K x 1024 spp is 8.5e9 samples
 };
 
 int make_params(const qgScene *sc, const qgRenderParams *rp, WfParams *P, Shard *sh)
@@ -529,6 +530,7 @@ int make_params(const qgScene *sc, const qgRenderParams *rp, WfParams *P, Shard 
     const int k = rp->tile_rank + lt * ranks, tx = k % sh->tiles_x, ty = k / sh->tiles_x;
     px += (unsigned long long) (std::min(W, tx * 4 + 4) - tx * 4) * (unsigned long long) (std::min(H, ty * 4 + 4) - ty * 4);
   }
+  sh->owned_pixels = px;
   sh->valid_samples = px * (unsigned long long) (s1 - s0);
   P->tiles_x = sh->tiles_x;
   P->tile_rank = rp->tile_rank;
@@ -793,7 +795,8 @@ int render_adaptive(qgScene *sc, const qgRenderParams *rp, float *d_accum, float
   KernelClock clk{sc, st, stats != nullptr};
   P.mode = 1;
   size_t trip_cap = 0;
-  uint32_t n_active = (uint32_t) sh.valid_samples / (uint32_t) std::max(1, spp_max);  // pixels this shard owns
+  // pixels this shard owns (valid_samples = pixels * spp is 64-bit: 4K x 1024 spp = 8.5e9 must not be narrowed first)
+  uint32_t n_active = (uint32_t) sh.owned_pixels;
   for (int round = 0; n_active > 0; ++round) {
     // first round: everyone needs sppMin samples; later rounds look 4 samples ahead
     int chunk = round == 0 ? spp_min : std::min(4, spp_max - spp_min);
@@ -811,6 +814,7 @@ int render_adaptive(qgScene *sc, const qgRenderParams *rp, float *d_accum, float
     CU(cudaMemcpyAsync(&na, d_nact.p, sizeof na, cudaMemcpyDeviceToHost, st));
     CU(cudaStreamSynchronize(st));
     launches += 1;
+    if ((size_t) na * (size_t) chunk > trip_cap) return fail(QG_EINVAL, "adaptive round larger than its buffers");
     n_active = na;
     if (na == 0) break;
     const size_t np = (size_t) na * (size_t) chunk;

@@ -42,7 +42,10 @@ class Renderer_B200 {
  protected:
   RendererParam &param;
   qgScene *scene = nullptr;
-  std::string assetDir;
+  qgMulti *multi = nullptr;  // -gpus N: one scene replica, host thread and NCCL rank per device (Renderer_MPI's rank model)
+  int numGpus = 1, tileSplit = 1;
+  std::string assetDir, rankImagePrefix;
+  bool saveRankImages = false;
   size_t pixelW = 0, pixelH = 0;
   size_t mpiSize = 1, mpiRank = 0;  // Renderer::mpiSize / mpiRank: the interleaved 4x4-tile shard (renderer.cpp:383-387)
  public:
@@ -54,17 +57,34 @@ class Renderer_B200 {
   ~Renderer_B200() { Terminate(); }
   void SetShard(size_t rank, size_t size) { mpiRank = rank; mpiSize = size; }
   void SetAssetDir(const std::string &d) { assetDir = d; }
+  // Renderer_MPI (src/renderers/Renderer_MPI.cpp:33-55) inside one process: G = gpus ranks, tileSplit = G_t of them share
+  // a sample range by the interleaved-tile rule, G / G_t sample ranges. rankImages: also write rank_<r>_*Buffer.png (:132-138)
+  void SetGpus(int gpus, int tile_split = 1, bool rankImages = false) { numGpus = gpus; tileSplit = tile_split; saveRankImages = rankImages; }
+  void SetRankImagePrefix(const std::string &p) { rankImagePrefix = p; }
   size_t W() const { return pixelW; }
   size_t H() const { return pixelH; }
 
   bool Init(int device = 0)
   {
     if (qg_init(device) != QG_OK) { fprintf(stderr, "Renderer_B200::Init: %s\n", qg_last_error()); return false; }
+    if (numGpus > 1) {  // devices device .. device + G - 1
+      std::vector<int32_t> devs((size_t) numGpus);
+      for (int g = 0; g < numGpus; ++g) devs[(size_t) g] = device + g;
+      if (qg_multi_create(devs.data(), numGpus, &multi) != QG_OK) { fprintf(stderr, "Renderer_B200::Init: %s\n", qg_last_error()); return false; }
+    }
     return true;
   }
   // LoadScene(filename): 1 on success, 0 on failure
   int LoadScene(const char *filename)
   {
+    if (multi) {
+      if (qg_multi_load_xml(multi, filename, assetDir.c_str()) != QG_OK) {
+        printf("Failed to load the file \"%s\": %s\n", filename, qg_last_error());
+        return 0;
+      }
+      scene = qg_multi_scene(multi, 0);  // owned by multi
+      return 1;
+    }
     if (scene) { qg_scene_destroy(scene); scene = nullptr; }
     if (qg_scene_load_xml(filename, assetDir.c_str(), &scene) != QG_OK) {
       printf("Failed to load the file \"%s\": %s\n", filename, qg_last_error());
@@ -103,6 +123,18 @@ class Renderer_B200 {
     rp.material_class = param.materialClass;
     rp.sort_by_material = param.sortByMaterial ? 1 : 0;
     rp.spp_min = param.sppMin < param.sppMax ? (int32_t) param.sppMin : 0;  // SuperSamplerHalton's adaptive stop
+    if (multi) {
+      if (mpiSize > 1) { fprintf(stderr, "Renderer_B200: -shard and -gpus do not combine\n"); return false; }
+      rp.tile_rank = 0;
+      rp.tile_ranks = 1;
+      const std::string pre = rankImagePrefix;
+      if (qg_multi_render(multi, &rp, tileSplit, saveRankImages ? pre.c_str() : nullptr, linearBuffer.data(), colorBuffer.data(), depthBuffer.data(),
+                          sampleCountBuffer.data(), maskBuffer.data(), &stats) != QG_OK) {
+        fprintf(stderr, "Renderer_B200::Render: %s\n", qg_last_error());
+        return false;
+      }
+      return true;
+    }
     if (qg_render(scene, &rp, linearBuffer.data(), colorBuffer.data(), depthBuffer.data(), sampleCountBuffer.data(), maskBuffer.data(),
                   &stats) != QG_OK) {
       fprintf(stderr, "Renderer_B200::Render: %s\n", qg_last_error());
@@ -110,16 +142,18 @@ class Renderer_B200 {
     }
     return true;
   }
-  // the PNG set of Renderer_MPI::Render (src/renderers/Renderer_MPI.cpp:134-138)
-  bool SaveImages(const std::string &prefix = "")
+  // the PNG set of Renderer_MPI::Render (src/renderers/Renderer_MPI.cpp:134-138,188-193): FrameBuffer::SaveImage, SaveZImage
+  // (depth normalised, framebuffer.cpp:62-86,113-135) and SaveSampleCountImage (sample counts stretched to 0..255, :88-107)
+  bool SaveImages(const std::string &prefix = "", const std::string &suffix = "")
   {
     const int w = (int) pixelW, h = (int) pixelH;
-    return qg_save_png_rgb8((prefix + "colorBuffer.png").c_str(), colorBuffer.data(), w, h) == QG_OK &&
-           qg_save_png_depth((prefix + "depthBuffer.png").c_str(), depthBuffer.data(), w, h) == QG_OK &&
-           qg_save_png_gray8((prefix + "sampleBuffer.png").c_str(), sampleCountBuffer.data(), w, h) == QG_OK;
+    return qg_save_png_rgb8((prefix + "colorBuffer" + suffix + ".png").c_str(), colorBuffer.data(), w, h) == QG_OK &&
+           qg_save_png_depth((prefix + "depthBuffer" + suffix + ".png").c_str(), depthBuffer.data(), w, h) == QG_OK &&
+           qg_save_png_sample_count((prefix + "sampleBuffer" + suffix + ".png").c_str(), sampleCountBuffer.data(), w, h) == QG_OK;
   }
   void Terminate()
   {
+    if (multi) { qg_multi_destroy(multi); multi = nullptr; scene = nullptr; }
     if (scene) { qg_scene_destroy(scene); scene = nullptr; }
   }
 };

@@ -578,10 +578,10 @@ __global__ void __launch_bounds__(256) k_mat_scatter(const DScene S, const WfBuf
 }
 void launch_mat_sort(const DScene &S, const WfBuffers &B, const WfParams &P, cudaStream_t st)
 {
-  k_mat_hist<<<148 * 4, 256, 0, st>>>(S, B, P);
+  k_mat_hist<<<qb_sms() * 4, 256, 0, st>>>(S, B, P);
   k_mat_scan<<<1, 32, 0, st>>>(B);
   static_assert(QB_MAT_BINS == 256, "k_mat_scatter uses one thread per bin");
-  k_mat_scatter<<<148 * 8, 256, 0, st>>>(S, B, P);
+  k_mat_scatter<<<qb_sms() * 8, 256, 0, st>>>(S, B, P);
 }
 
 // ---- adaptive sampling: SuperSamplerHalton (src/scene/scene.cpp:83-123) -----------------------------------------------------
@@ -683,6 +683,8 @@ void launch_wf_stats(const WfBuffers &B, int max_bounce, cudaStream_t st) { k_wf
 
 // persistent grid of one shade kernel: every SM filled to that kernel's own residency (the classes differ a lot in
 // registers, so one grid for all would hold the default class at the heaviest class's 3 blocks / SM)
+#define QB_SHADE_MAX_BLOCKS 4
+int wf_shade_grid_max() { return qb_sms() * QB_SHADE_MAX_BLOCKS; }
 static int persistent_grid_shade(const void *kernel)
 {
   int dev = 0, sms = 0, per_sm = 0;
@@ -690,7 +692,7 @@ static int persistent_grid_shade(const void *kernel)
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, QB_BLOCK, 0);
   if (per_sm < 1) per_sm = 1;
-  if (per_sm > 4) per_sm = 4;  // measured: 4 blocks / SM is the knee (xmas shade 104.7 / 92.9 / 93.5 ms at 3 / 4 / 5, tower 11.3 / 10.8 / 13.1)
+  if (per_sm > QB_SHADE_MAX_BLOCKS) per_sm = QB_SHADE_MAX_BLOCKS;  // measured: 4 blocks / SM is the knee (xmas shade 104.7 / 92.9 / 93.5 ms at 3 / 4 / 5, tower 11.3 / 10.8 / 13.1)
   if (const char *e = getenv("QB_SHADE_BLOCKS")) per_sm = std::max(1, std::min(per_sm, atoi(e)));  // A/B override
   return sms * per_sm;
 }

@@ -3,7 +3,7 @@
 // (oracle build: -O2 -ffp-contract=off). Division and sqrt are the IEEE-rounded defaults of nvcc
 // (-prec-div=true -prec-sqrt=true), denormals are kept (-ftz=false).
 //
-//   Scene::TraceNodeNormal / TraceNodeShadow   src/scene/scene.cpp:35-74      -> trace_closest / trace_any
+//   Scene::TraceNodeNormal / TraceNodeShadow   src/scene/scene.cpp:35-74      -> traverse_pool (traverse.cuh)
 //   Node::ToNodeCoords / FromNodeCoords        src/core/node.cpp:112-139      -> to_node / from_node
 //   Sphere::IntersectRay                       src/objects/objects.cpp:55-141
 //   Plane::IntersectRay                        src/objects/objects.cpp:149-208
@@ -120,26 +120,8 @@ __device__ __forceinline__ bool mesh_box_hit(const DMesh *__restrict__ m, const 
   return !(entry > t_max || entry > exit);
 }
 
-// IntersectTriangle up to the acceptance decision. N is the unit face normal the reference recomputes per test,
-// here computed once on the host with the same expression. Returns accepted t or a negative number.
-__device__ __forceinline__ float tri_t(const Ray3 &r, float z, V3 A, V3 B, V3 C, V3 N)
-{
-  const float dz = dot(r.d, N);
-  if (qabs(dz) < 1e-7f) return -1.f;
-  const float pz = dot(r.p - A, N);
-  const float t = -pz / dz;
-  if (t <= QB_BIAS) return -1.f;
-  if (!(z > t)) return -1.f;
-  const V3 p = r.p + t * r.d;
-  const int axis = tri_axis(N);
-  const float s = 1.f / tri_area(axis, A, B, C);
-  const float a = tri_area(axis, p, B, C) * s;
-  const float b = tri_area(axis, p, C, A) * s;
-  const float c = 1.f - a - b;
-  if (a < 0 || b < 0 || c < 0) return -1.f;
-  return t;
-}
-
+// IntersectTriangle's acceptance decision (objects.cpp:212-262). N is the unit face normal the reference recomputes per
+// test, here computed once on the host with the same expression.
 // The same decision without early exits: every lane of a converged LEAF phase runs one instruction stream. s and axis
 // are the per-triangle constants 1 / TriangleArea(axis, A, B, C) and the dropped axis, computed on the host with the
 // same expressions. Values computed past a failed check are never used (ok is false), so NaN/inf there are harmless.
@@ -185,99 +167,6 @@ __device__ __forceinline__ bool tri_candidate(const Ray3 &r, V3 A, V3 B, V3 C, V
   ok = ok && !(a < 0 || b < 0 || c < 0);
   t_out = t;
   return ok;
-}
-
-// TraceBVHNode. ANY = stop at the first accepted triangle (the reference finishes the traversal, but its
-// return value is the same boolean). Returns the slot of the last accepted triangle (closest) or -1; z updated.
-template <bool ANY>
-__device__ __forceinline__ int bvh_trace(const DScene &S, uint32_t root_ref, const Ray3 &r, float &z, int &uv_slot, float &uv_t,
-                                         TraceCounters &cnt)
-{
-  uint32_t stack[QB_STACK];
-  int sp = 0;
-  stack[sp++] = root_ref;
-  const V3 drcp = v3(1.f, 1.f, 1.f) / r.d;
-  const bool gx = qabs(r.d.x) < 1e-7f, gy = qabs(r.d.y) < 1e-7f, gz = qabs(r.d.z) < 1e-7f;
-  int best = -1;
-  while (sp != 0) {
-    const uint32_t ref = stack[--sp];
-    if (ref & QB_LEAF_BIT) {
-      const uint32_t base = ref & 0x0FFFFFFFu;
-      const uint32_t count = ((ref >> 28) & 7u) + 1u;
-      for (uint32_t i = 0; i < count; ++i) {
-        const DTri *tp = &S.tris[base + i];
-        const float4 ta = __ldg(&tp->a), tb = __ldg(&tp->b), tc = __ldg(&tp->c);
-        QB_CNT(tris);
-        const float t = tri_t(r, z, xyz(ta), xyz(tb), xyz(tc), v3(ta.w, tb.w, tc.w));
-        if (t > 0.f) {
-          z = t;
-          best = (int) (base + i);
-          if (ANY) return best;
-          // remember the last accepted triangle that carries texture coordinates (bit 31 of tri_face)
-          if (__ldg(&S.tri_face[base + i]) & 0x80000000u) { uv_slot = best; uv_t = t; }
-        }
-      }
-    } else {
-      const DBvhNode *np = &S.bvh[ref];
-      const float4 na = __ldg(&np->a), nb = __ldg(&np->b), nc = __ldg(&np->c);
-      const uint4 nd = __ldg(&np->d);
-      QB_CNT(nodes);
-      // p = -(rpos - bound) * drcp, per component; min/max per axis unless the axis is degenerate
-      const float p00x = -(r.p.x - na.x) * drcp.x, p00y = -(r.p.y - na.y) * drcp.y, p00z = -(r.p.z - na.z) * drcp.z;
-      const float p01x = -(r.p.x - na.w) * drcp.x, p01y = -(r.p.y - nb.x) * drcp.y, p01z = -(r.p.z - nb.y) * drcp.z;
-      const float p10x = -(r.p.x - nb.z) * drcp.x, p10y = -(r.p.y - nb.w) * drcp.y, p10z = -(r.p.z - nc.x) * drcp.z;
-      const float p11x = -(r.p.x - nc.y) * drcp.x, p11y = -(r.p.y - nc.z) * drcp.y, p11z = -(r.p.z - nc.w) * drcp.z;
-      const float t00x = gx ? -QB_BIGFLOAT : qmin(p00x, p01x), t01x = gx ? QB_BIGFLOAT : qmax(p00x, p01x);
-      const float t10x = gx ? -QB_BIGFLOAT : qmin(p10x, p11x), t11x = gx ? QB_BIGFLOAT : qmax(p10x, p11x);
-      const float t00y = gy ? -QB_BIGFLOAT : qmin(p00y, p01y), t01y = gy ? QB_BIGFLOAT : qmax(p00y, p01y);
-      const float t10y = gy ? -QB_BIGFLOAT : qmin(p10y, p11y), t11y = gy ? QB_BIGFLOAT : qmax(p10y, p11y);
-      const float t00z = gz ? -QB_BIGFLOAT : qmin(p00z, p01z), t01z = gz ? QB_BIGFLOAT : qmax(p00z, p01z);
-      const float t10z = gz ? -QB_BIGFLOAT : qmin(p10z, p11z), t11z = gz ? QB_BIGFLOAT : qmax(p10z, p11z);
-      const float t_max = z;
-      const float entry0 = qmax(t00x, qmax(t00y, t00z));
-      const float entry1 = qmax(t10x, qmax(t10y, t10z));
-      const float exit0 = qmin(t01x, qmin(t01y, t01z));
-      const float exit1 = qmin(t11x, qmin(t11y, t11z));
-      const bool h0 = (entry0 < t_max && entry0 < exit0);
-      const bool h1 = (entry1 < t_max && entry1 < exit1);
-      if (h0 && h1) {
-        if (entry0 < entry1) { stack[sp++] = nd.y; stack[sp++] = nd.x; }
-        else { stack[sp++] = nd.x; stack[sp++] = nd.y; }
-      } else if (h0) {
-        stack[sp++] = nd.x;
-      } else if (h1) {
-        stack[sp++] = nd.y;
-      }
-    }
-  }
-  return best;
-}
-
-// One object test in Scene::TraceNode* order. Returns true when hInfo would have been updated; slot = triangle slot.
-template <bool ANY>
-__device__ __forceinline__ bool object_test(const DScene &S, const DNode *__restrict__ n, const Ray3 &r, float &z, int &slot,
-                                            int &uv_slot, float &uv_t, TraceCounters &cnt)
-{
-  const int type = __ldg(&n->type);
-  QB_CNT(objects);
-  slot = -1;
-  if (type == QG_OBJ_SPHERE) {
-    const float t = sphere_t(r, z);
-    if (t > 0.f) { z = t; return true; }
-    return false;
-  }
-  if (type == QG_OBJ_PLANE) {
-    const float t = plane_t(r, z);
-    if (t > 0.f) { z = t; return true; }
-    return false;
-  }
-  const DMesh *m = &S.meshes[__ldg(&n->mesh)];
-  if (__ldg(&m->num_faces) == 0u) return false;
-  float mexit;
-  V3 drcp;
-  if (!mesh_box_hit(m, r, z, mexit, drcp)) return false;
-  slot = bvh_trace<ANY>(S, __ldg(&m->root_ref), r, z, uv_slot, uv_t, cnt);
-  return slot >= 0;
 }
 
 // ---- hit attributes ---------------------------------------------------------------------------------------------
@@ -415,79 +304,6 @@ __device__ __forceinline__ void hit_geometry(const DScene &S, int k, const DNode
   from_node(&S.nodes[0], p, N);
   h.p = p;
   h.N = N;
-}
-
-// ---- Scene::TraceNodeNormal -------------------------------------------------------------------------------------
-// c/x/y: world-space rays; with_diff=false treats x and y as absent (duvw = 0), the form used for secondary rays.
-// stale_tex: reproduce the reference's carry-over of uvw/duvw/hasTexture from an earlier, farther hit when the
-// closest hit is a triangle without texture coordinates (IntersectTriangle leaves those fields untouched).
-// Returns the object index (into obj_node) or -1; z = hit distance.
-__device__ __forceinline__ int trace_closest(const DScene &S, const Ray3 &c, const Ray3 &x, const Ray3 &y, bool with_diff,
-                                             bool stale_tex, float &z, HitAttr &h, TraceCounters &cnt)
-{
-  const DNode *root = &S.nodes[0];
-  const Ray3 c0 = to_node(root, c);
-  z = QB_BIGFLOAT;
-  int best_k = -1, best_slot = -1;
-  int tex_k = -1, tex_slot = -1, last_tri = -1;
-  float tex_t = 0.f;
-  for (int k = 0; k < S.num_obj; ++k) {
-    const DNode *n = &S.nodes[__ldg(&S.obj_node[k])];
-    const Ray3 r = chain_ray(S, k, c0);
-    int slot, uv_slot = -1;
-    float uv_t = 0.f;
-    if (object_test<false>(S, n, r, z, slot, uv_slot, uv_t, cnt)) {
-      best_k = k;
-      best_slot = slot;
-      if (slot >= 0) last_tri = slot;
-      if (slot < 0) { tex_k = k; tex_slot = -1; tex_t = z; }                    // sphere / plane always write uvw
-      else if (uv_slot >= 0) { tex_k = k; tex_slot = uv_slot; tex_t = uv_t; }   // last accepted triangle with uv
-    }
-  }
-  if (best_k < 0) return -1;
-  const DNode *n = &S.nodes[__ldg(&S.obj_node[best_k])];
-  const Ray3 r = chain_ray(S, best_k, c0);
-  hit_geometry(S, best_k, n, best_slot, z, r, h);
-  // Sphere/Plane::IntersectRay never write hInfo.mtlID: it keeps what an earlier, farther triangle hit left there
-  if (best_slot < 0 && last_tri >= 0 && stale_tex)
-    h.mtl_id = (__ldg(&S.faces[__ldg(&S.tri_face[last_tri]) & 0x7FFFFFFFu].mtl_uv) >> 1) - 1;
-  h.uvw = v3(0.5f, 0.5f, 0.5f);
-  h.duvw0 = v3(0.f);
-  h.duvw1 = v3(0.f);
-  h.has_texture = 0;
-  if (tex_k == best_k && tex_slot == best_slot) {
-    Ray3 rx = r, ry = r;
-    if (with_diff) {
-      rx = chain_ray(S, best_k, to_node(root, x));
-      ry = chain_ray(S, best_k, to_node(root, y));
-    }
-    h.has_texture = hit_texture(S, n, best_slot, z, r, rx, ry, with_diff, h.uvw, h.duvw0, h.duvw1) ? 1 : 0;
-  } else if (tex_k >= 0 && stale_tex) {
-    const DNode *tn = &S.nodes[__ldg(&S.obj_node[tex_k])];
-    const Ray3 tr = chain_ray(S, tex_k, c0);
-    Ray3 rx = tr, ry = tr;
-    if (with_diff) {
-      rx = chain_ray(S, tex_k, to_node(root, x));
-      ry = chain_ray(S, tex_k, to_node(root, y));
-    }
-    h.has_texture = hit_texture(S, tn, tex_slot, tex_t, tr, rx, ry, with_diff, h.uvw, h.duvw0, h.duvw1) ? 1 : 0;
-  }
-  return best_k;
-}
-
-// ---- Scene::TraceNodeShadow: any hit with bias < t < tmax ------------------------------------------------------
-__device__ __forceinline__ bool trace_any(const DScene &S, const Ray3 &c, float tmax, TraceCounters &cnt)
-{
-  const Ray3 c0 = to_node(&S.nodes[0], c);
-  float z = tmax;
-  for (int k = 0; k < S.num_obj; ++k) {
-    const DNode *n = &S.nodes[__ldg(&S.obj_node[k])];
-    const Ray3 r = chain_ray(S, k, c0);
-    int slot, uv_slot;
-    float uv_t;
-    if (object_test<true>(S, n, r, z, slot, uv_slot, uv_t, cnt)) return true;
-  }
-  return false;
 }
 
 }  // namespace qb

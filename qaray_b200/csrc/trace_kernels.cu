@@ -48,6 +48,13 @@ __device__ __forceinline__ void put_rec(float4 *r0, float4 *r1, uint32_t idx, co
   r0[idx] = f4(h.z, __int_as_float(h.k), __int_as_float(h.slot), __int_as_float(h.tex_slot));
   r1[idx] = f4(h.tex_t, __int_as_float(h.tex_k), __int_as_float(h.last_tri), 0.f);
 }
+// the same without touching r1.w: the cull-check pass keeps its flag bits there while a ray may be walked more than once
+__device__ __forceinline__ void put_rec_keep_w(float4 *r0, float4 *r1, uint32_t idx, const HitRec &h)
+{
+  r0[idx] = f4(h.z, __int_as_float(h.k), __int_as_float(h.slot), __int_as_float(h.tex_slot));
+  float *p = (float *) &r1[idx];
+  p[0] = h.tex_t; p[1] = __int_as_float(h.tex_k); p[2] = __int_as_float(h.last_tri);
+}
 __device__ __forceinline__ HitRec get_rec(const float4 *r0, const float4 *r1, uint32_t idx)
 {
   const float4 a = r0[idx], b = r1[idx];
@@ -111,6 +118,10 @@ struct WfClosestIO {
   }
   __device__ void store(uint32_t idx, const HitRec &h) { put_rec(B.h1, B.h2, idx, h); }  // h1/h2 double as the record until finish
   __device__ void store_any(uint32_t, bool) {}
+  // cull check: bit k of the record's spare word = "object k of this ray must be walked with the cull off" (k_redo_detect)
+  __device__ void store_redo(uint32_t idx, const HitRec &h) { put_rec_keep_w(B.h1, B.h2, idx, h); }
+  __device__ void flag(uint32_t idx, int k) const { if (k < 32) atomicOr((uint32_t *) &B.h2[idx].w, 1u << k); }
+  __device__ uint32_t flags(uint32_t idx) const { return __float_as_uint(B.h2[idx].w); }
 };
 
 struct WfShadowIO {
@@ -190,7 +201,10 @@ template <class IO> __device__ __forceinline__ void redo_detect(const DScene &S,
       float tt;
       if (tri_accept(r, z_entry, xyz(ta), xyz(tb), xyz(tc), v3(ta.w, tb.w, tc.w), td.x, __float_as_int(td.y), tt) && tt > t_box) any = true;
     }
-    if (any) Q.q[e].w = 1u;
+    if (any) {
+      Q.q[e].w = 1u;
+      io.flag(ent.x, k);
+    }
   }
 }
 // the flagged pairs' rays through the same traversal core with the cull off; records overwritten through the base IO
@@ -202,20 +216,29 @@ struct RedoIO {
   __device__ uint32_t count() const { return n; }
   __device__ uint32_t *cursor() { return Q.fetch; }
   __device__ uint32_t map(uint32_t q) const { return Q.q[q].w ? Q.q[q].x : 0xFFFFFFFFu; }
-  // the cull is off only for the (ray, mesh) pairs k_redo_detect flagged. Every other pair that drops boxes and finds
-  // nothing in this pass did so in the first pass too (h.z can only be smaller now) and was cleared there against a
-  // larger z, so it needs no second check: defer() swallows it
+  uint32_t mask = 0u;  // flagged objects of the ray this lane is walking (bit k = object k), read when the ray is loaded
+  // The cull is off only for the (ray, mesh) pairs k_redo_detect flagged: bit k of the ray's record word, the queue itself
+  // for objects beyond 32. Every other pair that drops boxes and finds nothing in this pass did so in the first pass too
+  // (h.z can only be smaller now) and was cleared there against a larger z, so it needs no second check: defer() swallows
+  // it — unless the first pass overflowed the queue: pairs that did not fit were repeated exactly inside their lane then,
+  // and are again now (defer() false), so an overflow costs time, never exactness.
   __device__ bool exact(uint32_t idx, int k) const
   {
+    if (k < 32) return (mask >> k) & 1u;
     for (uint32_t e = 0; e < n; ++e) {
       const uint4 ent = Q.q[e];
       if (ent.x == idx && (int) ent.y == k && ent.w) return true;
     }
     return false;
   }
-  __device__ bool defer(uint32_t, int, float) const { return true; }
-  __device__ bool load(uint32_t idx, Ray3 &c, float &tmax) { return idx != 0xFFFFFFFFu && base.load(idx, c, tmax); }
-  __device__ void store(uint32_t idx, const HitRec &h) { base.store(idx, h); }
+  __device__ bool defer(uint32_t, int, float) const { return *Q.count <= Q.cap; }
+  __device__ bool load(uint32_t idx, Ray3 &c, float &tmax)
+  {
+    if (idx == 0xFFFFFFFFu) return false;
+    mask = base.flags(idx);
+    return base.load(idx, c, tmax);
+  }
+  __device__ void store(uint32_t idx, const HitRec &h) { base.store_redo(idx, h); }
   __device__ void store_any(uint32_t, bool) {}
 };
 __device__ __forceinline__ RedoQueue wf_redo_queue(const WfBuffers &B, const WfParams &P)
@@ -416,6 +439,9 @@ struct RayBufClosestIO {
   }
   __device__ void store(uint32_t idx, const HitRec &h) { put_rec(r0, r1, idx, h); }
   __device__ void store_any(uint32_t, bool) {}
+  __device__ void store_redo(uint32_t idx, const HitRec &h) { put_rec_keep_w(r0, r1, idx, h); }
+  __device__ void flag(uint32_t idx, int k) const { if (k < 32) atomicOr((uint32_t *) &r1[idx].w, 1u << k); }
+  __device__ uint32_t flags(uint32_t idx) const { return __float_as_uint(r1[idx].w); }
 };
 
 struct RayBufAnyIO {
@@ -534,13 +560,13 @@ void launch_wf_trace(const DScene &S, const WfBuffers &B, const WfParams &P, int
   const int fg = P.depth == 0 ? fg_primary : fg_secondary;
   if (P.depth == 0) {
     k_wf_trace<true><<<grid, QB_BLOCK, 0, st>>>(S, B, P);
-    k_redo_detect<true><<<148 * 8, QB_BLOCK, 0, st>>>(S, B, P);
-    k_redo_exact<true><<<148, QB_BLOCK, 0, st>>>(S, B, P);
+    k_redo_detect<true><<<qb_sms() * 8, QB_BLOCK, 0, st>>>(S, B, P);
+    k_redo_exact<true><<<qb_sms(), QB_BLOCK, 0, st>>>(S, B, P);
     k_wf_finish<true><<<fg, QB_BLOCK, 0, st>>>(S, B, P);
   } else {
     k_wf_trace<false><<<grid, QB_BLOCK, 0, st>>>(S, B, P);
-    k_redo_detect<false><<<148 * 8, QB_BLOCK, 0, st>>>(S, B, P);
-    k_redo_exact<false><<<148, QB_BLOCK, 0, st>>>(S, B, P);
+    k_redo_detect<false><<<qb_sms() * 8, QB_BLOCK, 0, st>>>(S, B, P);
+    k_redo_exact<false><<<qb_sms(), QB_BLOCK, 0, st>>>(S, B, P);
     k_wf_finish<false><<<fg, QB_BLOCK, 0, st>>>(S, B, P);
   }
 }
@@ -551,12 +577,13 @@ void launch_wf_shadow(const DScene &S, const WfBuffers &B, const WfParams &P, in
 void launch_wf_area(const DScene &S, const WfBuffers &B, const WfParams &P, int grid, cudaStream_t st)
 {
   k_wf_area_shadow<<<grid, QB_BLOCK, 0, st>>>(S, B, P);
-  k_wf_area_resolve<<<148 * 8, QB_BLOCK, 0, st>>>(S, B, P);
+  k_wf_area_resolve<<<qb_sms() * 8, QB_BLOCK, 0, st>>>(S, B, P);
 }
 static int flat_grid(size_t n)
 {
   size_t g = (n + QB_BLOCK - 1) / QB_BLOCK;
-  if (g > 148 * 8) g = 148 * 8;
+  const size_t cap = (size_t) qb_sms() * 8;
+  if (g > cap) g = cap;
   if (g < 1) g = 1;
   return (int) g;
 }
@@ -587,10 +614,14 @@ void launch_trace_closest_rays(const DScene &S, const qgRay *rays, size_t n, qgH
   uint32_t *cur = (uint32_t *) scratch;
   float4 *r0 = (float4 *) ((char *) scratch + 16), *r1 = r0 + n;
   cudaMemsetAsync(cur, 0, 16, st);
-  RayBufClosestIO io{rays, (uint32_t) n, cur, r0, r1, RedoQueue{(uint4 *) (r1 + n), (uint32_t) n, cur + 1, cur + 2}};
+  // QB_REDO_CAP: test hook — a smaller cull-check queue than one entry per ray, so the overflow path (the lane repeats the
+  // mesh itself, first pass and redo pass alike) is exercised by the edge fixtures (tests/test_gpu_edges.py)
+  uint32_t redo_cap = (uint32_t) n;
+  if (const char *e = getenv("QB_REDO_CAP")) redo_cap = (uint32_t) std::min<size_t>(n, (size_t) std::max(0, atoi(e)));
+  RayBufClosestIO io{rays, (uint32_t) n, cur, r0, r1, RedoQueue{(uint4 *) (r1 + n), redo_cap, cur + 1, cur + 2}};
   k_trace_closest_rays<<<flat_grid(n), QB_BLOCK, 0, st>>>(S, io, stats);
-  k_redo_detect_rays<<<148 * 8, QB_BLOCK, 0, st>>>(S, io);
-  k_redo_exact_rays<<<148, QB_BLOCK, 0, st>>>(S, io, stats);
+  k_redo_detect_rays<<<qb_sms() * 8, QB_BLOCK, 0, st>>>(S, io);
+  k_redo_exact_rays<<<qb_sms(), QB_BLOCK, 0, st>>>(S, io, stats);
   k_finish_rays<<<flat_grid(n), QB_BLOCK, 0, st>>>(S, rays, (uint32_t) n, r0, r1, out);
 }
 void launch_trace_any_rays(const DScene &S, const float *rays6, const float *tmax, size_t n, uint8_t *occ, unsigned long long *stats,

@@ -457,7 +457,9 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
 }
 
 // Attributes of a finished closest-hit ray (what Scene::TraceNodeNormal leaves in DiffHitInfo::c): the tail of
-// trace_closest, run by full warps after the traversal. c/x/y world-space rays as in trace_closest.
+// traversal, run by full warps afterwards. c/x/y: world-space rays; with_diff = false treats x and y as absent (duvw = 0),
+// the form used for secondary rays. stale_tex: reproduce the reference's carry-over of uvw/duvw/hasTexture from an earlier,
+// farther hit when the closest hit is a triangle without texture coordinates (IntersectTriangle leaves those fields untouched).
 __device__ __forceinline__ void finish_hit(const DScene &S, const HitRec &rec, const Ray3 &c, const Ray3 &x, const Ray3 &y, bool with_diff,
                                            bool stale_tex, HitAttr &h, float *txy = nullptr)
 {

@@ -193,6 +193,15 @@ void launch_primary_rays(const WfParams &P, size_t n, qgRay *out, cudaStream_t s
 int wf_trace_grid();   // persistent grid sizes (blocks), from the occupancy calculator
 int wf_shadow_grid();
 int wf_shade_grid();
+int wf_shade_grid_max();  // upper bound of every shade kernel's grid (all material classes): sizes the dead-entry padding of the queues
+// SM count of the current device (grid sizes of the non-persistent helpers are multiples of it)
+inline int qb_sms()
+{
+  int dev = 0, sms = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  return sms > 0 ? sms : 1;
+}
 void upload_texture_taps(const float *xy64);  // 32 (x,y) tap offsets of Texture::Sample's elliptical filter
 
 

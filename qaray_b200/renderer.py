@@ -173,7 +173,7 @@ class Renderer_B200(object):
         W, H = self.pixelW, self.pixelH
         capi.check(lib, lib.qg_save_png_rgb8(os.fsencode(prefix + "colorBuffer.png"), _ptr(self.colorBuffer), W, H))
         capi.check(lib, lib.qg_save_png_depth(os.fsencode(prefix + "depthBuffer.png"), _ptr(self.depthBuffer), W, H))
-        capi.check(lib, lib.qg_save_png_gray8(os.fsencode(prefix + "sampleBuffer.png"), _ptr(self.sampleCountBuffer), W, H))
+        capi.check(lib, lib.qg_save_png_sample_count(os.fsencode(prefix + "sampleBuffer.png"), _ptr(self.sampleCountBuffer), W, H))
 
     def Terminate(self):
         if self.scene is not None:

@@ -41,6 +41,24 @@ def test_degenerate_direction_rays_match_reference(name):
     sc.close()
 
 
+@pytest.mark.parametrize("cap", [0, 1, 7])
+def test_cull_check_queue_overflow_stays_exact(cap, monkeypatch):
+    """QB_REDO_CAP forces the deferred cull-check queue (deviation 1) to overflow: pairs that do not fit are
+    repeated exactly inside their lane, in the first pass and in the redo pass alike (round-1 advice: a ray with one
+    queued and one overflowed pair must not lose the overflowed pair's exact result)."""
+    monkeypatch.setenv("QB_REDO_CAP", str(cap))
+    name = "trc_scene_tower"
+    g = load_golden("edge_" + name)
+    sc = Scene.load(scene_xml(name), ASSETS)
+    out = sc.trace_closest(rays18_to_struct(g["rays"], np.zeros(len(g["rays"]), np.int32)))
+    sc.close()
+    ref = g["hits"]
+    m = ref["hit"] == 1
+    assert np.array_equal(out["hit"], ref["hit"])
+    assert np.array_equal(out["node"][m], ref["node"][m]) and np.array_equal(out["face"][m], ref["face"][m])
+    assert np.array_equal(out["z"][m].view(np.uint32), ref["z"][m].view(np.uint32)), "hit distance not bit-equal"
+
+
 def test_zero_rays_and_zero_pixels_are_ok():
     sc = Scene.load(scene_xml("example_project3_sphere"), ASSETS)
     assert len(sc.trace_closest(np.zeros(0, capi.RAY_DTYPE))) == 0

@@ -105,3 +105,56 @@ def test_two_rank_reduce_equals_single_rank_sum():
         want[..., 3] += 1
     assert np.array_equal(got, want)
     assert (got[..., 3] == spp).all()
+
+
+def shard_size(W, H, p):
+    lib = capi.load()
+    cam = capi.Camera()
+    cam.width, cam.height = W, H
+    px, smp, paths = C.c_uint64(), C.c_uint64(), C.c_uint64()
+    capi.check(lib, lib.qg_shard_size(C.byref(cam), C.byref(p), C.byref(px), C.byref(smp), C.byref(paths)))
+    return px.value, smp.value, paths.value
+
+
+def test_shard_sizes_are_64_bit_at_4k_1024spp():
+    """BASELINE config 5 (3840x2160, 1024 spp): pixels * spp = 8.49e9 does not fit 32 bits. The adaptive driver once derived
+    its pixel count as (uint32) samples / spp = 4.1 M instead of 8.3 M and sized its buffers from it (round-1 advice)."""
+    W, H, spp = 3840, 2160, 1024
+    px, smp, paths = shard_size(W, H, capi.RenderParams(spp, 5, 1, 0, W, H, 0, 1, 0, 0, 0, 0, 0, 4))
+    assert px == W * H and smp == W * H * spp and smp > 2 ** 32 and paths == smp
+    # tile shards of the same job: owned pixels partition the frame, edge tiles counted by their real size
+    W, H = 3839, 2157
+    tot = 0
+    for r in range(8):
+        px, smp, paths = shard_size(W, H, capi.RenderParams(spp, 5, 1, 0, W, H, r, 8, 0, 0, 0, 0))
+        assert smp == px * spp and paths >= smp
+        tot += px
+    assert tot == W * H
+
+
+@pytest.mark.parametrize("nranks,tile_split", [(1, 1), (2, 1), (2, 2), (4, 2), (8, 2), (8, 8), (8, 1), (6, 3)])
+def test_shard_params_tile_x_sample_split_partitions_the_job(nranks, tile_split):
+    """qg_shard_params = G_t x G_s of SURVEY.md 8(e): every (pixel, sample) of the frame belongs to exactly one rank"""
+    lib = capi.load()
+    W, H, spp = 45, 31, 12
+    whole = capi.RenderParams(spp, 5, 1, 0, W, H, 0, 1, 0, 0, 0, 0)
+    total = np.zeros((H, W), np.int64)
+    for r in range(nranks):
+        mine = capi.RenderParams()
+        capi.check(lib, lib.qg_shard_params(C.byref(whole), r, nranks, tile_split, C.byref(mine)))
+        assert mine.tile_ranks == tile_split and mine.tile_rank == r % tile_split
+        total += coverage(W, H, spp, mine.tile_rank, mine.tile_ranks, mine.sample_begin, mine.sample_end)
+    assert (total == spp).all()
+
+
+def test_shard_params_rejects_bad_splits():
+    lib = capi.load()
+    whole = capi.RenderParams(8, 5, 1, 0, 16, 16, 0, 1, 0, 0, 0, 0)
+    out = capi.RenderParams()
+    assert lib.qg_shard_params(C.byref(whole), 0, 4, 3, C.byref(out)) == capi.QG_EINVAL      # G_t does not divide G
+    assert lib.qg_shard_params(C.byref(whole), 4, 4, 1, C.byref(out)) == capi.QG_EINVAL      # rank out of range
+    shard = capi.RenderParams(8, 5, 1, 0, 16, 16, 1, 2, 0, 0, 0, 0)
+    assert lib.qg_shard_params(C.byref(shard), 0, 2, 1, C.byref(out)) == capi.QG_EINVAL      # already a shard
+    adaptive = capi.RenderParams(8, 5, 1, 0, 16, 16, 0, 1, 0, 0, 0, 0, 0, 4)
+    assert lib.qg_shard_params(C.byref(adaptive), 0, 2, 1, C.byref(out)) == capi.QG_EINVAL   # adaptive stop needs all samples of a pixel
+    assert lib.qg_shard_params(C.byref(adaptive), 0, 2, 2, C.byref(out)) == capi.QG_OK
