@@ -123,7 +123,9 @@ def test_qg_multi_render_equals_qg_render(ndev, tile_split, tmp_path):
         for plane in ("color", "depth", "sample"):
             assert os.path.exists("%srank_%d_%sBuffer.png" % (prefix, r, plane))
     if ndev == 1:
-        assert np.array_equal(np.asarray(Image.open(prefix + "rank_0_colorBuffer.png").convert("RGB")), one[1])
+        # one rank: its plane IS the frame (the same accumulation buffer resolved twice; two renders differ by the order of
+        # the fp32 atomic additions, hence `many`, not `one`)
+        assert np.array_equal(np.asarray(Image.open(prefix + "rank_0_colorBuffer.png").convert("RGB")), many[1])
 
 
 def run_cli(args, cwd):
@@ -144,8 +146,8 @@ def test_cli_writes_the_reference_output_set(tmp_path):
     out = run_cli(["-batch", "-spp", str(spp), "-assets", ASSETS, "-out", str(tmp_path) + os.sep, scene_xml(name)], str(tmp_path))
     assert "Elapsed Time" in out
     one = single_render(lib, name, spp)
-    col = np.asarray(Image.open(str(tmp_path / "colorBuffer.png")).convert("RGB"))
-    assert np.array_equal(col, one[1])
+    col = np.asarray(Image.open(str(tmp_path / "colorBuffer.png")).convert("RGB")).astype(np.int32)
+    assert np.abs(col - one[1].astype(np.int32)).max() <= 1   # two renders: the fp32 atomic additions come in a different order
     z = one[2]
     hit = z != np.float32(1e30)
     zmin, zmax = z[hit].min(), z[hit].max()
