@@ -374,6 +374,7 @@ int upload_scene(qgScene *sc)
   D.materials = sc->materials.p; D.multi = sc->multi.p; D.lights = sc->lights.p; D.textures = sc->textures.p; D.texels = sc->texels.p;
   D.num_nodes = nn; D.num_obj = sc->num_obj; D.num_meshes = (int) meshes.size(); D.num_materials = (int) mats.size();
   D.num_lights = (int) lights.size(); D.num_textures = (int) texs.size(); D.num_nonambient = nonambient;
+  D.bvh_stack = std::max(1, sc->max_bvh_depth + 1);
   sc->dev_num_area = 0;
   for (const qgLight &l : F.lights)
     if ((l.type == QG_LIGHT_POINT || l.type == QG_LIGHT_SPOT) && l.size > 0.01f) sc->dev_num_area++;

@@ -107,6 +107,7 @@ struct DScene {
   const uchar4 *texels;
   int32_t num_nodes, num_obj, num_meshes, num_materials, num_lights, num_textures;
   int32_t num_nonambient;
+  int32_t bvh_stack;  // deferred far children a ray can hold at once = deepest mesh BVH of the scene + 1 (sizes the pool's stacks)
   DTexColor background, environment;
 };
 

@@ -9,10 +9,40 @@
 // Persistent kernels: grid = SMs x resident blocks; each warp pulls 32 consecutive rays from a device cursor, so
 // long rays do not hold back a statically assigned tail and no host sync is needed between bounces.
 #include "traverse.cuh"
+#include "blockpool.cuh"
 #include "wavefront.h"
 #include <algorithm>
+#include <mutex>
+#include <set>
+#include <utility>
+
+#ifndef QB_BLOCKPOOL
+#define QB_BLOCKPOOL 1  // 1: block-level ray pool (blockpool.cuh); 0: per-warp lane pool (traverse.cuh), kept for A/B
+#endif
 
 namespace qb {
+
+#if QB_BLOCKPOOL
+#define QB_TRACE_THREADS QB_BP_THREADS
+#define QB_TRACE_BOUNDS __launch_bounds__(QB_BP_THREADS, 2)
+#define QB_TRACE_BOUNDS_ANY __launch_bounds__(QB_BP_THREADS, 2)
+// the traversal of one kernel: scene table, then the block pool over dynamic shared memory
+#define QB_TRAVERSE(ANYHIT, io, cnt)                          \
+  extern __shared__ __align__(16) uint32_t s_pool[];          \
+  __shared__ SceneTab s_tab;                                  \
+  load_scene_tab(S, s_tab);                                   \
+  traverse_block<ANYHIT>(S, io, s_pool, S.bvh_stack, s_tab, cnt)
+#else
+#define QB_TRACE_THREADS QB_BLOCK
+#define QB_TRACE_BOUNDS __launch_bounds__(QB_BLOCK, QB_MIN_BLOCKS)
+#define QB_TRACE_BOUNDS_ANY __launch_bounds__(QB_BLOCK, QB_MIN_BLOCKS_ANY)
+#define QB_TRAVERSE(ANYHIT, io, cnt)                                       \
+  __shared__ uint32_t s_stack[QB_STACK * QB_BLOCK];                        \
+  __shared__ SceneTab s_tab;                                               \
+  __shared__ uint32_t s_coop[(QB_BLOCK / 32) * QB_COOP_SLOTS];             \
+  load_scene_tab(S, s_tab);                                                \
+  traverse_pool<ANYHIT>(S, io, s_stack, s_coop, s_tab, cnt)
+#endif
 
 __device__ __forceinline__ float4 f4(float x, float y, float z, float w) { return make_float4(x, y, z, w); }
 
@@ -155,15 +185,11 @@ struct WfShadowIO {
 
 // PRIMARY = depth 0 (rays generated in registers) / depth >= 1 (rays read from the path state): two instantiations.
 template <bool PRIMARY>
-__global__ void __launch_bounds__(QB_BLOCK, QB_MIN_BLOCKS) k_wf_trace(const DScene S, const WfBuffers B, const WfParams P)
+__global__ void QB_TRACE_BOUNDS k_wf_trace(const DScene S, const WfBuffers B, const WfParams P)
 {
-  __shared__ uint32_t s_stack[QB_STACK * QB_BLOCK];
-  __shared__ SceneTab s_tab;
-  __shared__ uint32_t s_coop[(QB_BLOCK / 32) * QB_COOP_SLOTS];
   TraceCounters cnt = {0, 0, 0};
   WfClosestIO<PRIMARY> io{B, P, PRIMARY ? P.n_paths : min(B.counters[QB_CNT_PATHS + P.depth], B.capacity)};
-  load_scene_tab(S, s_tab);
-  traverse_pool<false>(S, io, s_stack, s_coop, s_tab, cnt);
+  QB_TRAVERSE(false, io, cnt);
   flush_counters(B.stats, cnt);
 }
 
@@ -216,7 +242,6 @@ struct RedoIO {
   __device__ uint32_t count() const { return n; }
   __device__ uint32_t *cursor() { return Q.fetch; }
   __device__ uint32_t map(uint32_t q) const { return Q.q[q].w ? Q.q[q].x : 0xFFFFFFFFu; }
-  uint32_t mask = 0u;  // flagged objects of the ray this lane is walking (bit k = object k), read when the ray is loaded
   // The cull is off only for the (ray, mesh) pairs k_redo_detect flagged: bit k of the ray's record word, the queue itself
   // for objects beyond 32. Every other pair that drops boxes and finds nothing in this pass did so in the first pass too
   // (h.z can only be smaller now) and was cleared there against a larger z, so it needs no second check: defer() swallows
@@ -224,7 +249,7 @@ struct RedoIO {
   // and are again now (defer() false), so an overflow costs time, never exactness.
   __device__ bool exact(uint32_t idx, int k) const
   {
-    if (k < 32) return (mask >> k) & 1u;
+    if (k < 32) return (base.flags(idx) >> k) & 1u;
     for (uint32_t e = 0; e < n; ++e) {
       const uint4 ent = Q.q[e];
       if (ent.x == idx && (int) ent.y == k && ent.w) return true;
@@ -232,12 +257,7 @@ struct RedoIO {
     return false;
   }
   __device__ bool defer(uint32_t, int, float) const { return *Q.count <= Q.cap; }
-  __device__ bool load(uint32_t idx, Ray3 &c, float &tmax)
-  {
-    if (idx == 0xFFFFFFFFu) return false;
-    mask = base.flags(idx);
-    return base.load(idx, c, tmax);
-  }
+  __device__ bool load(uint32_t idx, Ray3 &c, float &tmax) { return idx != 0xFFFFFFFFu && base.load(idx, c, tmax); }
   __device__ void store(uint32_t idx, const HitRec &h) { base.store_redo(idx, h); }
   __device__ void store_any(uint32_t, bool) {}
 };
@@ -253,18 +273,14 @@ __global__ void __launch_bounds__(QB_BLOCK) k_redo_detect(const DScene S, const 
   redo_detect(S, io, wf_redo_queue(B, P));
 }
 template <bool PRIMARY>
-__global__ void __launch_bounds__(QB_BLOCK, QB_MIN_BLOCKS) k_redo_exact(const DScene S, const WfBuffers B, const WfParams P)
+__global__ void QB_TRACE_BOUNDS k_redo_exact(const DScene S, const WfBuffers B, const WfParams P)
 {
-  __shared__ uint32_t s_stack[QB_STACK * QB_BLOCK];
-  __shared__ SceneTab s_tab;
-  __shared__ uint32_t s_coop[(QB_BLOCK / 32) * QB_COOP_SLOTS];
   const uint32_t n = min(B.counters[QB_CNT_REDO + P.depth], B.redo_capacity);
   if (n == 0u) return;
   TraceCounters cnt = {0, 0, 0};
   WfClosestIO<PRIMARY> base{B, P, 0u};
   RedoIO<WfClosestIO<PRIMARY>> io{base, wf_redo_queue(B, P), n};
-  load_scene_tab(S, s_tab);
-  traverse_pool<false>(S, io, s_stack, s_coop, s_tab, cnt);
+  QB_TRAVERSE(false, io, cnt);
   flush_counters(B.stats, cnt);
 }
 
@@ -313,15 +329,11 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_finish(const DScene S, const Wf
   }
 }
 
-__global__ void __launch_bounds__(QB_BLOCK, QB_MIN_BLOCKS_ANY) k_wf_shadow(const DScene S, const WfBuffers B, const WfParams P)
+__global__ void QB_TRACE_BOUNDS_ANY k_wf_shadow(const DScene S, const WfBuffers B, const WfParams P)
 {
-  __shared__ uint32_t s_stack[QB_STACK * QB_BLOCK];
-  __shared__ SceneTab s_tab;
-  __shared__ uint32_t s_coop[(QB_BLOCK / 32) * QB_COOP_SLOTS];
   TraceCounters cnt = {0, 0, 0};
   WfShadowIO io{B, P, min(B.counters[QB_CNT_SHADOW + P.depth], B.shadow_capacity)};
-  load_scene_tab(S, s_tab);
-  traverse_pool<true>(S, io, s_stack, s_coop, s_tab, cnt);
+  QB_TRAVERSE(true, io, cnt);
   flush_counters(B.stats, cnt, 5);
 }
 
@@ -361,15 +373,11 @@ struct WfAreaIO {
   }
 };
 
-__global__ void __launch_bounds__(QB_BLOCK, QB_MIN_BLOCKS_ANY) k_wf_area_shadow(const DScene S, const WfBuffers B, const WfParams P)
+__global__ void QB_TRACE_BOUNDS_ANY k_wf_area_shadow(const DScene S, const WfBuffers B, const WfParams P)
 {
-  __shared__ uint32_t s_stack[QB_STACK * QB_BLOCK];
-  __shared__ SceneTab s_tab;
-  __shared__ uint32_t s_coop[(QB_BLOCK / 32) * QB_COOP_SLOTS];
   TraceCounters cnt = {0, 0, 0};
   WfAreaIO io{S, B, P, min(B.counters[QB_CNT_AREA + P.depth], B.area_capacity) * (uint32_t) QB_AREA_SPP_MAX};
-  load_scene_tab(S, s_tab);
-  traverse_pool<true>(S, io, s_stack, s_coop, s_tab, cnt);
+  QB_TRAVERSE(true, io, cnt);
   flush_counters(B.stats, cnt, 5);
 }
 
@@ -465,14 +473,10 @@ struct RayBufAnyIO {
   __device__ void store_any(uint32_t idx, bool occluded) { occ[idx] = occluded ? 1 : 0; }
 };
 
-__global__ void __launch_bounds__(QB_BLOCK) k_trace_closest_rays(const DScene S, RayBufClosestIO io, unsigned long long *stats)
+__global__ void QB_TRACE_BOUNDS k_trace_closest_rays(const DScene S, RayBufClosestIO io, unsigned long long *stats)
 {
-  __shared__ uint32_t s_stack[QB_STACK * QB_BLOCK];
-  __shared__ SceneTab s_tab;
-  __shared__ uint32_t s_coop[(QB_BLOCK / 32) * QB_COOP_SLOTS];
   TraceCounters cnt = {0, 0, 0};
-  load_scene_tab(S, s_tab);
-  traverse_pool<false>(S, io, s_stack, s_coop, s_tab, cnt);
+  QB_TRAVERSE(false, io, cnt);
   flush_counters(stats, cnt);
 }
 
@@ -509,14 +513,10 @@ __global__ void __launch_bounds__(QB_BLOCK) k_finish_rays(const DScene S, const 
   }
 }
 
-__global__ void __launch_bounds__(QB_BLOCK) k_trace_any_rays(const DScene S, RayBufAnyIO io, unsigned long long *stats)
+__global__ void QB_TRACE_BOUNDS_ANY k_trace_any_rays(const DScene S, RayBufAnyIO io, unsigned long long *stats)
 {
-  __shared__ uint32_t s_stack[QB_STACK * QB_BLOCK];
-  __shared__ SceneTab s_tab;
-  __shared__ uint32_t s_coop[(QB_BLOCK / 32) * QB_COOP_SLOTS];
   TraceCounters cnt = {0, 0, 0};
-  load_scene_tab(S, s_tab);
-  traverse_pool<true>(S, io, s_stack, s_coop, s_tab, cnt);
+  QB_TRAVERSE(true, io, cnt);
   flush_counters(stats, cnt, 5);
 }
 
@@ -544,39 +544,77 @@ static int persistent_grid(const void *kernel)
   if (per_sm < 1) per_sm = 1;
   return sms * per_sm;
 }
+#if QB_BLOCKPOOL
+// Traversal kernels run over the block pool: QB_BP_THREADS threads and bp_smem_bytes(stack entries of the scene) of dynamic
+// shared memory per block, two blocks per SM. The opt-in above 48 KB is per kernel and per device.
+static size_t trace_smem(const DScene &S) { return bp_smem_bytes(S.bvh_stack); }
+template <class K> static void trace_attr(K kernel)
+{
+  // keyed by (kernel, device): instantiations of one template share their function type, so a per-type flag would not do
+  static std::mutex mu;
+  static std::set<std::pair<const void *, int>> done;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!done.insert({(const void *) kernel, dev}).second) return;
+  cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, QB_BP_SMEM);
+}
+static int trace_grid_for(size_t rays)  // persistent grid, smaller when the launch holds fewer rays than the pools
+{
+  const size_t full = (size_t) qb_sms() * 2;
+  const size_t need = (rays + QB_BP_THREADS - 1) / QB_BP_THREADS;
+  return (int) std::max<size_t>(1, std::min(full, need));
+}
+int wf_trace_grid() { return qb_sms() * 2; }
+int wf_shadow_grid() { return qb_sms() * 2; }
+#define QB_LAUNCH_TRACE(kernel, grid, st, ...)                                         \
+  do {                                                                                 \
+    trace_attr(kernel);                                                                \
+    kernel<<<(grid), QB_BP_THREADS, trace_smem(S), (st)>>>(__VA_ARGS__);               \
+  } while (0)
+#else
+static int trace_grid_for(size_t rays)
+{
+  size_t g = (rays + QB_BLOCK - 1) / QB_BLOCK;
+  const size_t cap = (size_t) qb_sms() * 8;
+  return (int) std::max<size_t>(1, std::min(g, cap));
+}
 int wf_trace_grid()
 {
   static int g = std::min(persistent_grid((const void *) k_wf_trace<true>), persistent_grid((const void *) k_wf_trace<false>));
   return g;
 }
 int wf_shadow_grid() { static int g = persistent_grid((const void *) k_wf_shadow); return g; }
+#define QB_LAUNCH_TRACE(kernel, grid, st, ...) kernel<<<(grid), QB_BLOCK, 0, (st)>>>(__VA_ARGS__)
+#endif
 
 void launch_wf_trace(const DScene &S, const WfBuffers &B, const WfParams &P, int grid, cudaStream_t st)
 {
-  // traversal by the lane pool, then the hit attributes by full warps
+  // traversal by the ray pool, then the hit attributes by full warps
   // grid-stride kernels sized to what is resident at once (96 registers: 5 blocks / SM): a larger grid runs its last blocks
   // alone at low occupancy
   static const int fg_primary = persistent_grid((const void *) k_wf_finish<true>), fg_secondary = persistent_grid((const void *) k_wf_finish<false>);
   const int fg = P.depth == 0 ? fg_primary : fg_secondary;
+  const int redo_grid = QB_BLOCKPOOL ? qb_sms() / 4 : qb_sms();
   if (P.depth == 0) {
-    k_wf_trace<true><<<grid, QB_BLOCK, 0, st>>>(S, B, P);
+    QB_LAUNCH_TRACE(k_wf_trace<true>, grid, st, S, B, P);
     k_redo_detect<true><<<qb_sms() * 8, QB_BLOCK, 0, st>>>(S, B, P);
-    k_redo_exact<true><<<qb_sms(), QB_BLOCK, 0, st>>>(S, B, P);
+    QB_LAUNCH_TRACE(k_redo_exact<true>, redo_grid, st, S, B, P);
     k_wf_finish<true><<<fg, QB_BLOCK, 0, st>>>(S, B, P);
   } else {
-    k_wf_trace<false><<<grid, QB_BLOCK, 0, st>>>(S, B, P);
+    QB_LAUNCH_TRACE(k_wf_trace<false>, grid, st, S, B, P);
     k_redo_detect<false><<<qb_sms() * 8, QB_BLOCK, 0, st>>>(S, B, P);
-    k_redo_exact<false><<<qb_sms(), QB_BLOCK, 0, st>>>(S, B, P);
+    QB_LAUNCH_TRACE(k_redo_exact<false>, redo_grid, st, S, B, P);
     k_wf_finish<false><<<fg, QB_BLOCK, 0, st>>>(S, B, P);
   }
 }
 void launch_wf_shadow(const DScene &S, const WfBuffers &B, const WfParams &P, int grid, cudaStream_t st)
 {
-  k_wf_shadow<<<grid, QB_BLOCK, 0, st>>>(S, B, P);
+  QB_LAUNCH_TRACE(k_wf_shadow, grid, st, S, B, P);
 }
 void launch_wf_area(const DScene &S, const WfBuffers &B, const WfParams &P, int grid, cudaStream_t st)
 {
-  k_wf_area_shadow<<<grid, QB_BLOCK, 0, st>>>(S, B, P);
+  QB_LAUNCH_TRACE(k_wf_area_shadow, grid, st, S, B, P);
   k_wf_area_resolve<<<qb_sms() * 8, QB_BLOCK, 0, st>>>(S, B, P);
 }
 static int flat_grid(size_t n)
@@ -592,17 +630,13 @@ __global__ void __launch_bounds__(QB_BLOCK) k_redo_detect_rays(const DScene S, R
   if (*io.Q.count == 0u) return;
   redo_detect(S, io, io.Q);
 }
-__global__ void __launch_bounds__(QB_BLOCK, QB_MIN_BLOCKS) k_redo_exact_rays(const DScene S, RayBufClosestIO base, unsigned long long *stats)
+__global__ void QB_TRACE_BOUNDS k_redo_exact_rays(const DScene S, RayBufClosestIO base, unsigned long long *stats)
 {
-  __shared__ uint32_t s_stack[QB_STACK * QB_BLOCK];
-  __shared__ SceneTab s_tab;
-  __shared__ uint32_t s_coop[(QB_BLOCK / 32) * QB_COOP_SLOTS];
   const uint32_t n = min(*base.Q.count, base.Q.cap);
   if (n == 0u) return;
   TraceCounters cnt = {0, 0, 0};
   RedoIO<RayBufClosestIO> io{base, base.Q, n};
-  load_scene_tab(S, s_tab);
-  traverse_pool<false>(S, io, s_stack, s_coop, s_tab, cnt);
+  QB_TRAVERSE(false, io, cnt);
   flush_counters(stats, cnt);
 }
 // scratch: a 16-byte header (work cursor, cull-check count, cull-check cursor), two float4 records per ray, then the
@@ -619,9 +653,9 @@ void launch_trace_closest_rays(const DScene &S, const qgRay *rays, size_t n, qgH
   uint32_t redo_cap = (uint32_t) n;
   if (const char *e = getenv("QB_REDO_CAP")) redo_cap = (uint32_t) std::min<size_t>(n, (size_t) std::max(0, atoi(e)));
   RayBufClosestIO io{rays, (uint32_t) n, cur, r0, r1, RedoQueue{(uint4 *) (r1 + n), redo_cap, cur + 1, cur + 2}};
-  k_trace_closest_rays<<<flat_grid(n), QB_BLOCK, 0, st>>>(S, io, stats);
+  QB_LAUNCH_TRACE(k_trace_closest_rays, trace_grid_for(n), st, S, io, stats);
   k_redo_detect_rays<<<qb_sms() * 8, QB_BLOCK, 0, st>>>(S, io);
-  k_redo_exact_rays<<<qb_sms(), QB_BLOCK, 0, st>>>(S, io, stats);
+  QB_LAUNCH_TRACE(k_redo_exact_rays, QB_BLOCKPOOL ? qb_sms() / 4 : qb_sms(), st, S, io, stats);
   k_finish_rays<<<flat_grid(n), QB_BLOCK, 0, st>>>(S, rays, (uint32_t) n, r0, r1, out);
 }
 void launch_trace_any_rays(const DScene &S, const float *rays6, const float *tmax, size_t n, uint8_t *occ, unsigned long long *stats,
@@ -630,7 +664,7 @@ void launch_trace_any_rays(const DScene &S, const float *rays6, const float *tma
   uint32_t *cur = (uint32_t *) scratch;
   cudaMemsetAsync(cur, 0, 16, st);
   RayBufAnyIO io{rays6, tmax, (uint32_t) n, cur, occ};
-  k_trace_any_rays<<<flat_grid(n), QB_BLOCK, 0, st>>>(S, io, stats);
+  QB_LAUNCH_TRACE(k_trace_any_rays, trace_grid_for(n), st, S, io, stats);
 }
 void launch_primary_rays(const WfParams &P, size_t n, qgRay *out, cudaStream_t st)
 {

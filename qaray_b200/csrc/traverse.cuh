@@ -31,6 +31,9 @@ namespace qb {
 #endif
 #define QB_COOP_SLOTS 128          // (ray, triangle) pairs a warp's LEAF phase handles per round
 #define QB_REF_EMPTY 0x7FFFFFFFu   // "no current node" (an internal index never reaches 2^31-1)
+#ifndef QB_NEXT_REPS
+#define QB_NEXT_REPS 4             // objects per vote while the group between objects holds together
+#endif
 #ifndef QB_INNER_REPS
 #define QB_INNER_REPS 3            // node visits per vote while the inner group holds together
 #endif
@@ -380,8 +383,15 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
 #endif
     } else if (w_next >= w_fetch) {
       // ---- NEXT: the object just traversed reports its result, then the next object of the list is set up ----------
+      // Up to QB_NEXT_REPS objects per vote while at least half of the lanes that started are still between objects (a
+      // plane / sphere test or a missed mesh box leaves the lane in this state): a ray crosses the whole object list in a
+      // few NEXT phases instead of one per object.
+#pragma unroll 1
+      for (int rep = 0; rep < QB_NEXT_REPS; ++rep) {
+      const bool go_next = active && cur == QB_REF_EMPTY;
+      if (rep > 0 && 2 * __popc(__ballot_sync(0xFFFFFFFFu, go_next)) < n_next) break;
       bool redo = false;
-      if (s_next && k > 0 && cull_state == 1) {
+      if (go_next && k > 0 && cull_state == 1) {
         // the cull dropped boxes and the mesh produced no hit inside its own box: repeat it exactly as the reference walks it
         cull_state = 0;
         // closest-hit rays of the wavefront hand the check to k_redo_detect / k_redo_exact (trace_kernels.cu) and go on: a
@@ -394,7 +404,7 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
           cur = __float_as_uint(obj_rec(S, T, k - 1).lo.w);
         }
       }
-      if (s_next && !redo) {
+      if (go_next && !redo) {
         if (k > 0 && obj_slot >= 0) {
           h.k = k - 1; h.slot = obj_slot; h.last_tri = obj_slot;
           if (uv_slot >= 0) { h.tex_k = k - 1; h.tex_slot = uv_slot; h.tex_t = uv_t; }
@@ -432,6 +442,7 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
             }
           }
         }
+      }
       }
     } else {
       // ---- FETCH: idle lanes take consecutive rays from the device cursor (one atomic per warp) -------------------------
