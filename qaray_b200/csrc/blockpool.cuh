@@ -32,11 +32,17 @@ namespace qb {
 #define QB_BP_WARPS 8                 // warps per block; two blocks per SM (shadow(d) runs beside trace(d + 1))
 #endif
 #define QB_BP_THREADS (QB_BP_WARPS * 32)
+#ifndef QB_BP_BLOCKS
+#define QB_BP_BLOCKS 2                // resident blocks per SM
+#endif
 #ifndef QB_BP_SMEM
 #define QB_BP_SMEM (100 * 1024)       // dynamic shared memory per block: pool state + stacks
 #endif
 #ifndef QB_BP_INNER_REPS
 #define QB_BP_INNER_REPS 16           // node visits per vote (lanes refill from their column between visits)
+#endif
+#ifndef QB_BP_REFILL
+#define QB_BP_REFILL 8                // idle lanes that trigger a refill of the INNER loop
 #endif
 #ifndef QB_BP_MIN_LANES
 #define QB_BP_MIN_LANES 12            // the INNER loop ends when fewer lanes than this still hold a ray
@@ -184,28 +190,43 @@ __device__ __forceinline__ void traverse_block(const DScene &S, IO &io, uint32_t
       uint32_t cur = QB_REF_EMPTY, flags = 0u;
       int sp = 0;
 #pragma unroll 1
+      bool done = false;  // this lane's ray has left the phase (a leaf, or its mesh is finished): handed on at the next refill
       for (int rep = 0; rep < QB_BP_INNER_REPS; ++rep) {
-        if (row < 0) {  // take (another) inner ray of this column
-          const uint32_t m = rep == 0 ? aI : bp_ld(&P.avail[BP_INNER * 32 + lane]);
-          row = bp_claim(P, BP_INNER, lane, m, start);
+        // Hand-over and refill are batched: with a lane or two at a time they cost as many issue slots as a node visit
+        // (ncu: 20 % of the kernel's instructions at 5-7 of 32 lanes). Lanes whose ray has left wait until QB_BP_REFILL
+        // lanes are idle, then all of them pass their ray on and take the next inner ray of their column.
+        const int n_idle = __popc(__ballot_sync(FULL, row < 0 || done));
+        if (rep == 0 || n_idle >= QB_BP_REFILL) {
+          if (done) {
+            ST(F_CUR) = cur;
+            ST(F_SP) = (uint32_t) sp;
+            ST(F_FLAGS) = flags;
+            bp_release(P, bp_phase_of(cur), lane, row);
+            row = -1;
+            done = false;
+          }
+          if (row < 0) {
+            const uint32_t m = rep == 0 ? aI : bp_ld(&P.avail[BP_INNER * 32 + lane]);
+            row = bp_claim(P, BP_INNER, lane, m, start);
 #ifdef QB_BP_DEBUG
-          if (row >= 0) ++claims;
+            if (row >= 0) ++claims;
 #endif
-          if (row >= 0) {
-            __threadfence_block();
-            r.p = v3(STF(F_RPX), STF(F_RPY), STF(F_RPZ));
-            drcp = v3(STF(F_DCX), STF(F_DCY), STF(F_DCZ));
-            z = STF(F_Z);
-            cur = ST(F_CUR);
-            sp = (int) ST(F_SP);
-            flags = ST(F_FLAGS);
-            if (flags & 7u) {
-              r.d = v3(STF(F_RDX), STF(F_RDY), STF(F_RDZ));
-              mesh_exit = STF(F_MEXIT);
+            if (row >= 0) {
+              __threadfence_block();
+              r.p = v3(STF(F_RPX), STF(F_RPY), STF(F_RPZ));
+              drcp = v3(STF(F_DCX), STF(F_DCY), STF(F_DCZ));
+              z = STF(F_Z);
+              cur = ST(F_CUR);
+              sp = (int) ST(F_SP);
+              flags = ST(F_FLAGS);
+              if (flags & 7u) {
+                r.d = v3(STF(F_RDX), STF(F_RDY), STF(F_RDZ));
+                mesh_exit = STF(F_MEXIT);
+              }
             }
           }
         }
-        const bool go = row >= 0;
+        const bool go = row >= 0 && !done;
         if (go) {
           const DBvhNode *np = &S.bvh[cur];
           const float4 na = __ldg(&np->a), nb = __ldg(&np->b), nc = __ldg(&np->c);
@@ -284,25 +305,19 @@ __device__ __forceinline__ void traverse_block(const DScene &S, IO &io, uint32_t
             if (pop) popped = STK(sp);
             cur = none ? popped : near_ref;
           }
-          if (cur == QB_REF_EMPTY || (cur & QB_LEAF_BIT)) {  // the ray leaves this phase: hand it on
-            ST(F_CUR) = cur;
-            ST(F_SP) = (uint32_t) sp;
-            ST(F_FLAGS) = flags;
-            bp_release(P, bp_phase_of(cur), lane, row);
-            row = -1;
-          }
+          done = cur == QB_REF_EMPTY || (cur & QB_LEAF_BIT) != 0u;  // the ray leaves this phase
         }
         // Go on while enough lanes still hold a ray, or while inner nodes are all the block has to do. The test comes AFTER
         // the visit: a claimed ray always advances before it is handed back (two warps that claimed and returned the same
         // rays without visiting them — each failing its first claim while the other held them — ran in lockstep for ever).
-        const int held = __popc(__ballot_sync(FULL, row >= 0));
+        const int held = __popc(__ballot_sync(FULL, row >= 0 && !done));
         if (held == 0 || (held < QB_BP_MIN_LANES && !alone)) break;
       }
-      if (row >= 0) {  // still on an inner node when the loop ended
+      if (row >= 0) {  // whatever this lane still holds goes back to the pool, in the phase it is in now
         ST(F_CUR) = cur;
         ST(F_SP) = (uint32_t) sp;
         ST(F_FLAGS) = flags;
-        bp_release(P, BP_INNER, lane, row);
+        bp_release(P, bp_phase_of(cur), lane, row);
       }
     } else if (w_leaf >= w_next && w_leaf >= w_fetch) {
       // ---- LEAF: the leaves' triangles, pooled over the warp (see traverse.cuh) --------------------------------------

@@ -24,8 +24,8 @@ namespace qb {
 
 #if QB_BLOCKPOOL
 #define QB_TRACE_THREADS QB_BP_THREADS
-#define QB_TRACE_BOUNDS __launch_bounds__(QB_BP_THREADS, 2)
-#define QB_TRACE_BOUNDS_ANY __launch_bounds__(QB_BP_THREADS, 2)
+#define QB_TRACE_BOUNDS __launch_bounds__(QB_BP_THREADS, QB_BP_BLOCKS)
+#define QB_TRACE_BOUNDS_ANY __launch_bounds__(QB_BP_THREADS, QB_BP_BLOCKS)
 // the traversal of one kernel: scene table, then the block pool over dynamic shared memory
 #define QB_TRAVERSE(ANYHIT, io, cnt)                          \
   extern __shared__ __align__(16) uint32_t s_pool[];          \
@@ -561,12 +561,12 @@ template <class K> static void trace_attr(K kernel)
 }
 static int trace_grid_for(size_t rays)  // persistent grid, smaller when the launch holds fewer rays than the pools
 {
-  const size_t full = (size_t) qb_sms() * 2;
+  const size_t full = (size_t) qb_sms() * QB_BP_BLOCKS;
   const size_t need = (rays + QB_BP_THREADS - 1) / QB_BP_THREADS;
   return (int) std::max<size_t>(1, std::min(full, need));
 }
-int wf_trace_grid() { return qb_sms() * 2; }
-int wf_shadow_grid() { return qb_sms() * 2; }
+int wf_trace_grid() { return qb_sms() * QB_BP_BLOCKS; }
+int wf_shadow_grid() { return qb_sms() * QB_BP_BLOCKS; }
 #define QB_LAUNCH_TRACE(kernel, grid, st, ...)                                         \
   do {                                                                                 \
     trace_attr(kernel);                                                                \
