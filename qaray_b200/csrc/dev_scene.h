@@ -21,7 +21,7 @@ namespace qb {
 #define QB_MAX_DEPTH 8      // scene-tree depth supported by the chain replay
 #define QB_BLOCK 128        // threads per block of every persistent kernel
 #ifndef QB_MIN_BLOCKS
-#define QB_MIN_BLOCKS 6      // resident blocks per SM of the closest-hit kernels (80 registers; at 8 = 64 registers they spill and gain nothing)
+#define QB_MIN_BLOCKS 8      // resident blocks per SM of the closest-hit kernels: 64 registers, possible since the lanes' cold state lives in shared memory (traverse.cuh)
 #endif
 #ifndef QB_MIN_BLOCKS_ANY
 #define QB_MIN_BLOCKS_ANY 8  // any-hit kernels keep less state: 64 registers without spills, 7 % faster than at 6 (measured)

@@ -12,12 +12,14 @@
 #include "blockpool.cuh"
 #include "wavefront.h"
 #include <algorithm>
+#include <map>
 #include <mutex>
 #include <set>
+#include <tuple>
 #include <utility>
 
 #ifndef QB_BLOCKPOOL
-#define QB_BLOCKPOOL 1  // 1: block-level ray pool (blockpool.cuh); 0: per-warp lane pool (traverse.cuh), kept for A/B
+#define QB_BLOCKPOOL 0  // 0: per-warp lane pool (traverse.cuh); 1: block-level ray pool (blockpool.cuh), measured 20 % slower, kept for A/B
 #endif
 
 namespace qb {
@@ -36,12 +38,12 @@ namespace qb {
 #define QB_TRACE_THREADS QB_BLOCK
 #define QB_TRACE_BOUNDS __launch_bounds__(QB_BLOCK, QB_MIN_BLOCKS)
 #define QB_TRACE_BOUNDS_ANY __launch_bounds__(QB_BLOCK, QB_MIN_BLOCKS_ANY)
-#define QB_TRAVERSE(ANYHIT, io, cnt)                                       \
-  __shared__ uint32_t s_stack[QB_STACK * QB_BLOCK];                        \
-  __shared__ SceneTab s_tab;                                               \
-  __shared__ uint32_t s_coop[(QB_BLOCK / 32) * QB_COOP_SLOTS];             \
-  load_scene_tab(S, s_tab);                                                \
-  traverse_pool<ANYHIT>(S, io, s_stack, s_coop, s_tab, cnt)
+// dynamic shared memory: the lanes' stacks (as deep as the scene's deepest BVH), their cold state, the leaf scratch
+#define QB_TRAVERSE(ANYHIT, io, cnt)                          \
+  extern __shared__ __align__(16) uint32_t s_dyn[];           \
+  __shared__ SceneTab s_tab;                                  \
+  load_scene_tab(S, s_tab);                                   \
+  traverse_pool<ANYHIT>(S, io, s_dyn, s_tab, cnt)
 #endif
 
 __device__ __forceinline__ float4 f4(float x, float y, float z, float w) { return make_float4(x, y, z, w); }
@@ -573,19 +575,41 @@ int wf_shadow_grid() { return qb_sms() * QB_BP_BLOCKS; }
     kernel<<<(grid), QB_BP_THREADS, trace_smem(S), (st)>>>(__VA_ARGS__);               \
   } while (0)
 #else
+static size_t trace_smem(const DScene &S) { return lanepool_smem_bytes(S.bvh_stack); }
+// resident blocks of a traversal kernel for the scene's shared-memory need, cached per (kernel, bytes, device)
+template <class K> static int trace_blocks_per_sm(K kernel, size_t smem)
+{
+  static std::mutex mu;
+  static std::map<std::tuple<const void *, size_t, int>, int> cache;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  std::lock_guard<std::mutex> lock(mu);
+  const auto key = std::make_tuple((const void *) kernel, smem, dev);
+  auto it = cache.find(key);
+  if (it != cache.end()) return it->second;
+  if (smem > 48 * 1024) cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+  int per_sm = 0;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, QB_BLOCK, smem);
+  if (per_sm < 1) per_sm = 1;
+  cache[key] = per_sm;
+  return per_sm;
+}
 static int trace_grid_for(size_t rays)
 {
   size_t g = (rays + QB_BLOCK - 1) / QB_BLOCK;
   const size_t cap = (size_t) qb_sms() * 8;
   return (int) std::max<size_t>(1, std::min(g, cap));
 }
-int wf_trace_grid()
-{
-  static int g = std::min(persistent_grid((const void *) k_wf_trace<true>), persistent_grid((const void *) k_wf_trace<false>));
-  return g;
-}
-int wf_shadow_grid() { static int g = persistent_grid((const void *) k_wf_shadow); return g; }
-#define QB_LAUNCH_TRACE(kernel, grid, st, ...) kernel<<<(grid), QB_BLOCK, 0, (st)>>>(__VA_ARGS__)
+int wf_trace_grid() { return 0; }   // persistent grids are sized at launch: they depend on the scene's stack depth
+int wf_shadow_grid() { return 0; }
+// grid <= 0: persistent grid = SMs x resident blocks
+#define QB_LAUNCH_TRACE(kernel, grid, st, ...)                                                        \
+  do {                                                                                                \
+    const size_t smem_ = trace_smem(S);                                                               \
+    const int per_sm_ = trace_blocks_per_sm(kernel, smem_);                                           \
+    const int grid_ = (grid) > 0 ? std::min((int) (grid), qb_sms() * per_sm_) : qb_sms() * per_sm_;   \
+    kernel<<<grid_, QB_BLOCK, smem_, (st)>>>(__VA_ARGS__);                                            \
+  } while (0)
 #endif
 
 void launch_wf_trace(const DScene &S, const WfBuffers &B, const WfParams &P, int grid, cudaStream_t st)

@@ -35,7 +35,7 @@ namespace qb {
 #define QB_NEXT_REPS 4             // objects per vote while the group between objects holds together
 #endif
 #ifndef QB_INNER_REPS
-#define QB_INNER_REPS 3            // node visits per vote while the inner group holds together
+#define QB_INNER_REPS 5            // node visits per vote while the inner group holds together (A/B: 3 -> 5 -0.9 ms per tower step)
 #endif
 
 // what the closest-hit traversal leaves per ray; attributes are computed later by finish_hit (full warps)
@@ -166,31 +166,44 @@ __device__ __forceinline__ bool mesh_box_hit_q(const ObjRec &o, const Ray3 &r, f
 //   bool load(uint32_t idx, Ray3 &c, float &tmax)    world-space ray; false = padding entry (skipped, store not called)
 //   void store(uint32_t idx, const HitRec &)     closest
 //   void store_any(uint32_t idx, bool occluded)  any-hit
+// Words of a lane's COLD state, kept in shared memory ([word][thread], thread-private: no synchronisation, no bank
+// conflicts): what only the NEXT phase (a few times per ray) or a rare branch touches. With these 17 values in registers
+// the closest-hit kernels needed 80 registers (6 blocks / SM); without them they fit 64 and run 8 blocks / SM — a third
+// more warps to hide the node and triangle loads behind (long_scoreboard was the top stall).
+enum {
+  CW_C0PX = 0, CW_C0PY, CW_C0PZ, CW_C0DX, CW_C0DY, CW_C0DZ,        // the ray in the root node's space
+  CW_HK, CW_HSLOT, CW_HTEXK, CW_HTEXSLOT, CW_HTEXT, CW_HLASTTRI,  // HitRec without z
+  CW_ZENTRY, CW_ZSANE, CW_MEXIT,                                  // degenerate-axis cull of the current mesh
+  CW_UVSLOT, CW_UVT,                                              // last accepted triangle with uv inside the current object
+  CW_COUNT
+};
+// shared memory of one block of a traversal kernel, in words: stack[entries][QB_BLOCK], cold[CW_COUNT][QB_BLOCK], leaf scratch
+__host__ __device__ inline size_t lanepool_smem_bytes(int entries) { return 4u * ((size_t) (entries + CW_COUNT) * QB_BLOCK + (QB_BLOCK / 32) * QB_COOP_SLOTS); }
+
 template <bool ANY, class IO>
-__device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t *__restrict__ s_stack, uint32_t *__restrict__ s_coop,
-                                              const SceneTab &T, TraceCounters &cnt)
+__device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t *__restrict__ s_dyn, const SceneTab &T, TraceCounters &cnt)
 {
   const int lane = threadIdx.x & 31;
   const uint32_t lt_mask = (1u << lane) - 1u;
   const uint32_t n = io.count();
-  uint32_t *stk = s_stack + threadIdx.x;  // entry e at stk[e * QB_BLOCK]
+  uint32_t *stk = s_dyn + threadIdx.x;  // entry e at stk[e * QB_BLOCK]
+  uint32_t *cold = s_dyn + S.bvh_stack * QB_BLOCK + threadIdx.x;
+  uint32_t *s_coop = s_dyn + (S.bvh_stack + CW_COUNT) * QB_BLOCK;
+#define CW(f) cold[(f) * QB_BLOCK]
+#define CWF(f) __uint_as_float(cold[(f) * QB_BLOCK])
 
   bool active = false, exhausted = false;
   uint32_t idx = 0;
-  Ray3 c0, r;
+  Ray3 r;
   V3 drcp = v3(0.f);
   bool gx = false, gy = false, gz = false;
-  float mesh_exit = 0.f;  // where the ray leaves the current mesh's box (bounds the degenerate-axis cull below)
-  float z_entry = 0.f;    // h.z when the current mesh was entered
-  float z_sane = 0.f;     // hits of the current mesh beyond this distance can only be rounding artefacts (see the cull below)
   int cull_state = 0;     // 0 nothing dropped by the cull yet, 1 something dropped, 2 cull off (exact repeat of the mesh)
   int k = 0, sp = 0;
   uint32_t cur = QB_REF_EMPTY;
-  HitRec h;
-  h.z = 0.f; h.k = -1; h.slot = -1; h.tex_k = -1; h.tex_slot = -1; h.tex_t = 0.f; h.last_tri = -1;
-  int uv_slot = -1;   // last accepted triangle with uv inside the CURRENT object
-  float uv_t = 0.f;
+  float hz = 0.f;     // HitRec::z, the running hit distance (the rest of the record is cold)
   int obj_slot = -1;  // last accepted triangle inside the current object
+  // cold: CW_ZENTRY = hz when the current mesh was entered, CW_ZSANE = hits of the current mesh beyond this distance can only
+  // be rounding artefacts, CW_MEXIT = where the ray leaves the current mesh's box (bounds the degenerate-axis cull below)
 
   // Every lane is in one of four states; each iteration the warp votes and runs ONE phase, the one most lanes wait
   // for, with all of those lanes converged in it. Lanes in other states keep their state until their phase wins.
@@ -224,7 +237,7 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
           const float p01x = -(r.p.x - na.w) * drcp.x, p01y = -(r.p.y - nb.x) * drcp.y, p01z = -(r.p.z - nb.y) * drcp.z;
           const float p10x = -(r.p.x - nb.z) * drcp.x, p10y = -(r.p.y - nb.w) * drcp.y, p10z = -(r.p.z - nc.x) * drcp.z;
           const float p11x = -(r.p.x - nc.y) * drcp.x, p11y = -(r.p.y - nc.z) * drcp.y, p11z = -(r.p.z - nc.w) * drcp.z;
-          const float t_max = h.z;
+          const float t_max = hz;
           float entry0, entry1, exit0, exit1;
           bool h0, h1;
           if (!(gx || gy || gz)) {
@@ -260,7 +273,7 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
             // hit. So if something was dropped and the ray leaves the mesh with z still beyond z_sane = max(box exit,
             // 1000 box diagonals) — in practice: still without any hit — the mesh is traversed again with the cull off
             // (cull_state 2), exactly as the reference walks it. A ray that already holds a real hit never pays this.
-            const float t_far = qmin(t_max, mesh_exit);
+            const float t_far = qmin(t_max, CWF(CW_MEXIT));
             const bool h0r = h0, h1r = h1;
             if (cull_state != 2) {
             if (gx) {
@@ -321,11 +334,11 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
           const float4 ta = __ldg(&tp->a), tb = __ldg(&tp->b), tc = __ldg(&tp->c), td = __ldg(&tp->d);
           QB_CNT(tris);
           float t;
-          if (tri_accept(r, h.z, xyz(ta), xyz(tb), xyz(tc), v3(ta.w, tb.w, tc.w), td.x, __float_as_int(td.y), t)) {
+          if (tri_accept(r, hz, xyz(ta), xyz(tb), xyz(tc), v3(ta.w, tb.w, tc.w), td.x, __float_as_int(td.y), t)) {
             if (ANY) { io.store_any(idx, true); active = false; break; }
-            h.z = t;
+            hz = t;
             obj_slot = (int) (base + i);
-            if (__float_as_uint(td.z) & 0x80000000u) { uv_slot = obj_slot; uv_t = t; }
+            if (__float_as_uint(td.z) & 0x80000000u) { CW(CW_UVSLOT) = (uint32_t) obj_slot; CW(CW_UVT) = __float_as_uint(t); }
           }
         }
       }
@@ -370,11 +383,11 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
           for (uint32_t i = 0; i < count; ++i) {
             const uint32_t w = scr[excl + i];
             const float t = __uint_as_float(w);
-            if (!(w & 0x80000000u) && h.z > t) {
+            if (!(w & 0x80000000u) && hz > t) {
               if (ANY) { io.store_any(idx, true); active = false; break; }
-              h.z = t;
+              hz = t;
               obj_slot = (int) (lbase + i);
-              if (__ldg(&S.tri_face[lbase + i]) & 0x80000000u) { uv_slot = obj_slot; uv_t = t; }
+              if (__ldg(&S.tri_face[lbase + i]) & 0x80000000u) { CW(CW_UVSLOT) = (uint32_t) obj_slot; CW(CW_UVT) = __float_as_uint(t); }
             }
           }
         }
@@ -396,48 +409,63 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
         cull_state = 0;
         // closest-hit rays of the wavefront hand the check to k_redo_detect / k_redo_exact (trace_kernels.cu) and go on: a
         // single lane repeating a whole mesh costs up to ~30 ms, and some sample ranges hold a few dozen such rays
-        if (!(h.z <= z_sane) && (ANY || !io.defer(idx, k - 1, z_entry))) {
+        const float z_entry = CWF(CW_ZENTRY);
+        if (!(hz <= CWF(CW_ZSANE)) && (ANY || !io.defer(idx, k - 1, z_entry))) {
           redo = true;
           cull_state = 2;
-          h.z = z_entry;
-          obj_slot = -1; uv_slot = -1; sp = 0;
+          hz = z_entry;
+          obj_slot = -1; CW(CW_UVSLOT) = 0xFFFFFFFFu; sp = 0;
           cur = __float_as_uint(obj_rec(S, T, k - 1).lo.w);
         }
       }
       if (go_next && !redo) {
-        if (k > 0 && obj_slot >= 0) {
-          h.k = k - 1; h.slot = obj_slot; h.last_tri = obj_slot;
-          if (uv_slot >= 0) { h.tex_k = k - 1; h.tex_slot = uv_slot; h.tex_t = uv_t; }
-          obj_slot = -1;
+        if (!ANY && k > 0 && obj_slot >= 0) {
+          CW(CW_HK) = (uint32_t) (k - 1); CW(CW_HSLOT) = (uint32_t) obj_slot; CW(CW_HLASTTRI) = (uint32_t) obj_slot;
+          const uint32_t uv_slot = CW(CW_UVSLOT);
+          if ((int) uv_slot >= 0) { CW(CW_HTEXK) = (uint32_t) (k - 1); CW(CW_HTEXSLOT) = uv_slot; CW(CW_HTEXT) = CW(CW_UVT); }
         }
+        obj_slot = -1;
         if (k == S.num_obj) {
-          if (ANY) io.store_any(idx, false); else io.store(idx, h);
+          if (ANY) {
+            io.store_any(idx, false);
+          } else {
+            HitRec h;
+            h.z = hz; h.k = (int) CW(CW_HK); h.slot = (int) CW(CW_HSLOT); h.tex_k = (int) CW(CW_HTEXK); h.tex_slot = (int) CW(CW_HTEXSLOT);
+            h.tex_t = CWF(CW_HTEXT); h.last_tri = (int) CW(CW_HLASTTRI);
+            io.store(idx, h);
+          }
           active = false;
         } else {
           const ObjRec o = obj_rec(S, T, k);
+          Ray3 c0;
+          c0.p = v3(CWF(CW_C0PX), CWF(CW_C0PY), CWF(CW_C0PZ));
+          c0.d = v3(CWF(CW_C0DX), CWF(CW_C0DY), CWF(CW_C0DZ));
           r = chain_ray_tab(S, T, o, k, c0);
           const int type = o.id.x;
           QB_CNT(objects);
           ++k;
-          obj_slot = -1; uv_slot = -1;
+          CW(CW_UVSLOT) = 0xFFFFFFFFu;
           if (type == QG_OBJ_MESH) {
             const uint32_t root_ref = __float_as_uint(o.lo.w);
-            if (root_ref != QB_NO_FACES && mesh_box_hit_q(o, r, h.z, mesh_exit, drcp)) {
+            float mesh_exit;
+            if (root_ref != QB_NO_FACES && mesh_box_hit_q(o, r, hz, mesh_exit, drcp)) {
               cur = root_ref;
               cull_state = io.exact(idx, k - 1) ? 2 : 0;  // k was advanced above: k - 1 is this object
-              z_entry = h.z;
-              z_sane = qmax(mesh_exit * 1.001f, o.hi.w);
+              CW(CW_ZENTRY) = __float_as_uint(hz);
+              CW(CW_ZSANE) = __float_as_uint(qmax(mesh_exit * 1.001f, o.hi.w));
+              CW(CW_MEXIT) = __float_as_uint(mesh_exit);
               gx = qabs(r.d.x) < 1e-7f; gy = qabs(r.d.y) < 1e-7f; gz = qabs(r.d.z) < 1e-7f;
             }
           } else {
-            const float t = type == QG_OBJ_SPHERE ? sphere_t(r, h.z) : plane_t(r, h.z);
+            const float t = type == QG_OBJ_SPHERE ? sphere_t(r, hz) : plane_t(r, hz);
             if (t > 0.f) {
               if (ANY) {
                 io.store_any(idx, true);
                 active = false;
               } else {
-                h.z = t; h.k = k - 1; h.slot = -1;
-                h.tex_k = k - 1; h.tex_slot = -1; h.tex_t = t;  // sphere / plane always write uvw
+                hz = t;
+                CW(CW_HK) = (uint32_t) (k - 1); CW(CW_HSLOT) = 0xFFFFFFFFu;
+                CW(CW_HTEXK) = (uint32_t) (k - 1); CW(CW_HTEXSLOT) = 0xFFFFFFFFu; CW(CW_HTEXT) = __float_as_uint(t);  // sphere / plane always write uvw
               }
             }
           }
@@ -457,14 +485,23 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
         const uint32_t ray = my < n ? io.map(my) : my;
         if (my < n && io.load(ray, c, tmax)) {
           idx = ray;
-          c0 = to_node_tab(S, T, 0, c);
-          h.z = tmax; h.k = -1; h.slot = -1; h.tex_k = -1; h.tex_slot = -1; h.tex_t = 0.f; h.last_tri = -1;
-          k = 0; sp = 0; cur = QB_REF_EMPTY; obj_slot = -1; uv_slot = -1;
+          const Ray3 c0 = to_node_tab(S, T, 0, c);
+          CW(CW_C0PX) = __float_as_uint(c0.p.x); CW(CW_C0PY) = __float_as_uint(c0.p.y); CW(CW_C0PZ) = __float_as_uint(c0.p.z);
+          CW(CW_C0DX) = __float_as_uint(c0.d.x); CW(CW_C0DY) = __float_as_uint(c0.d.y); CW(CW_C0DZ) = __float_as_uint(c0.d.z);
+          hz = tmax;
+          if (!ANY) {
+            CW(CW_HK) = 0xFFFFFFFFu; CW(CW_HSLOT) = 0xFFFFFFFFu; CW(CW_HTEXK) = 0xFFFFFFFFu; CW(CW_HTEXSLOT) = 0xFFFFFFFFu;
+            CW(CW_HTEXT) = 0u; CW(CW_HLASTTRI) = 0xFFFFFFFFu;
+          }
+          CW(CW_UVSLOT) = 0xFFFFFFFFu;
+          k = 0; sp = 0; cur = QB_REF_EMPTY; obj_slot = -1;
           active = true;
         }
       }
     }
   }
+#undef CW
+#undef CWF
 }
 
 // Attributes of a finished closest-hit ray (what Scene::TraceNodeNormal leaves in DiffHitInfo::c): the tail of
