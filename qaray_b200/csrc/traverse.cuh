@@ -160,6 +160,27 @@ __device__ __forceinline__ bool mesh_box_hit_q(const ObjRec &o, const Ray3 &r, f
   return !(entry > t_max || entry > exit);
 }
 
+// Boxes behind the ray. The reference's slab test accepts a box the ray's LINE crosses behind its origin (entry < exit < 0,
+// objects.cpp:353-376 has no `exit >= 0`), so it walks about as many nodes behind a ray as in front of it; every triangle
+// there is then rejected by `t <= bias` (objects.cpp:227). Not visiting such a box changes no hit, no distance and no order
+// among the remaining visits, PROVIDED no triangle inside it could be accepted — which rounding can break in one way only:
+// a triangle whose plane passes within rounding noise of the origin gets a t = -pz/dz of arbitrary sign. Hence the margin:
+// a box is dropped only if, on some axis, all of it lies behind the origin by more than delta = 1e-4 * (|p| + box extent)
+// (rounding noise of pz is ~1e-7 of the same scale). Then for a triangle in it, either that axis is the one its projection
+// drops — its plane is then more than delta / sqrt(3) from the origin on the far side, t comes out negative — or the axis
+// is kept, and every point of the forward ray is outside the triangle's bounds by more than delta, so the barycentric
+// test rejects it (its own rounding is ~1e-6 relative). In the ray's parameter the condition is exit < -delta_a * |1/d_a|;
+// behind_bound returns the most negative of the three, one number per (ray, mesh). Rays with a degenerate axis take the
+// other slab path and are not culled this way.
+__device__ __forceinline__ float behind_bound(const ObjRec &o, const Ray3 &r, const V3 &drcp)
+{
+  if (qabs(r.d.x) < 1e-7f || qabs(r.d.y) < 1e-7f || qabs(r.d.z) < 1e-7f) return -QB_BIGFLOAT;
+  const float dx = (qabs(r.p.x) + qmax(qabs(o.lo.x), qabs(o.hi.x))) * qabs(drcp.x);
+  const float dy = (qabs(r.p.y) + qmax(qabs(o.lo.y), qabs(o.hi.y))) * qabs(drcp.y);
+  const float dz = (qabs(r.p.z) + qmax(qabs(o.lo.z), qabs(o.hi.z))) * qabs(drcp.z);
+  return -1e-4f * qmax(dx, qmax(dy, dz));
+}
+
 // IO concept:
 //   uint32_t count() const                       number of rays
 //   uint32_t *cursor()                           device work cursor
@@ -201,6 +222,7 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
   int k = 0, sp = 0;
   uint32_t cur = QB_REF_EMPTY;
   float hz = 0.f;     // HitRec::z, the running hit distance (the rest of the record is cold)
+  float bcull = -QB_BIGFLOAT;  // boxes the ray leaves before this (negative) parameter lie behind its origin: see behind_bound
   int obj_slot = -1;  // last accepted triangle inside the current object
   // cold: CW_ZENTRY = hz when the current mesh was entered, CW_ZSANE = hits of the current mesh beyond this distance can only
   // be rounding artefacts, CW_MEXIT = where the ray leaves the current mesh's box (bounds the degenerate-axis cull below)
@@ -247,8 +269,9 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
             entry1 = fmaxf(fminf(p10x, p11x), fmaxf(fminf(p10y, p11y), fminf(p10z, p11z)));
             exit0 = fminf(fmaxf(p00x, p01x), fminf(fmaxf(p00y, p01y), fmaxf(p00z, p01z)));
             exit1 = fminf(fmaxf(p10x, p11x), fminf(fmaxf(p10y, p11y), fmaxf(p10z, p11z)));
-            h0 = (entry0 < t_max && entry0 < exit0);
-            h1 = (entry1 < t_max && entry1 < exit1);
+            // ... and boxes that lie behind the ray's origin by more than the margin of behind_bound are not visited
+            h0 = (entry0 < t_max && entry0 < exit0) && !(exit0 < bcull);
+            h1 = (entry1 < t_max && entry1 < exit1) && !(exit1 < bcull);
           } else {
             const float t00x = gx ? -QB_BIGFLOAT : qmin(p00x, p01x), t01x = gx ? QB_BIGFLOAT : qmax(p00x, p01x);
             const float t10x = gx ? -QB_BIGFLOAT : qmin(p10x, p11x), t11x = gx ? QB_BIGFLOAT : qmax(p10x, p11x);
@@ -448,7 +471,7 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
           if (type == QG_OBJ_MESH) {
             const uint32_t root_ref = __float_as_uint(o.lo.w);
             float mesh_exit;
-            if (root_ref != QB_NO_FACES && mesh_box_hit_q(o, r, hz, mesh_exit, drcp)) {
+            if (root_ref != QB_NO_FACES && mesh_box_hit_q(o, r, hz, mesh_exit, drcp) && !(mesh_exit < (bcull = behind_bound(o, r, drcp)))) {
               cur = root_ref;
               cull_state = io.exact(idx, k - 1) ? 2 : 0;  // k was advanced above: k - 1 is this object
               CW(CW_ZENTRY) = __float_as_uint(hz);
