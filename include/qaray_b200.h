@@ -156,6 +156,8 @@ typedef struct qgRenderParams {
                              compile-time alias, src/materials/materials.h:57-61); 0 = MtlBlinn_PhotonMap, its default */
   int32_t spp_min; /* RendererParam::sppMin when below spp (= sppMax): SuperSamplerHalton's adaptive stop
                       (src/scene/scene.cpp:92-97); 0 or spp = fixed sample count */
+  int32_t use_photon_map; /* Scene::usePhotonMap (`-use-photon-map`, src/main.cpp:35): diffuse hits gather from the maps
+                             qg_photon_maps_build made (MtlBlinn_PhotonMap.cpp:341-352,426-458); material_class 0 only */
 } qgRenderParams;
 
 typedef struct qgRenderStats {
@@ -242,6 +244,44 @@ int qg_shard_coverage(const qgCamera *camera, const qgRenderParams *params, uint
  * pixels the shard owns, samples = pixels x its sample range (PixelRender loop iterations, renderer.cpp:310), and path
  * slots enumerated (16 per 4x4 tile, edge tiles padded). Any output may be NULL. */
 int qg_shard_size(const qgCamera *camera, const qgRenderParams *params, uint64_t *pixels, uint64_t *samples, uint64_t *paths);
+
+/* ---- photon / caustics maps: the emission pass of Renderer::ComputeScene (src/renderers/renderer.cpp:118-291) -------------
+ * Photons leave the point lights (the only IsPhotonSource, src/lights/lights.h:114), are traced with Scene::TraceNodeNormal,
+ * stored at diffuse surfaces from their second segment on, and continued by MtlBlinn_PhotonMap::RandomPhotonBounce
+ * (src/materials/MtlBlinn_PhotonMap.cpp:503-575) until the map holds `size` photons; powers are then divided by the number
+ * of emissions that stored something. Defaults = RendererParam's (src/renderers/renderer.h:52-57). */
+typedef struct qgPhotonParams {
+  int32_t photon_map_size, photon_map_bounce;     /* 10000, 20 */
+  float photon_map_radius;                        /* 0.2 */
+  int32_t caustics_map_size, caustics_map_bounce; /* 1000, 20 */
+  float caustics_map_radius;                      /* 1.0 */
+  uint32_t seed;                                  /* stream seed of the counter-based RNG (emission e has its own stream) */
+} qgPhotonParams;
+typedef struct qgPhotonStats {
+  uint64_t photons[2];   /* stored: [0] photon map, [1] caustics map */
+  uint64_t emitted[2];   /* numOfEmittedRays: emissions that stored at least one photon (the power normalisation) */
+  uint64_t emissions[2]; /* emissions traced */
+  uint64_t rays[2];      /* Scene::TraceNodeNormal calls */
+  double device_ms;
+} qgPhotonStats;
+/* builds both maps for the scene and keeps them with it (Renderer::ComputeScene); a render with use_photon_map = 1 needs them.
+ * A scene without point lights, or a size of 0, leaves the maps empty (the reference skips the pass, renderer.cpp:120-123). */
+int qg_photon_maps_build(qgScene *scene, const qgPhotonParams *params, qgPhotonStats *stats);
+/* Renderer::Terminate: scene->photonmap.Clear(); scene->causticsmap.Clear() */
+void qg_photon_maps_clear(qgScene *scene);
+/* The photons of map `which` (0 photon map, 1 caustics map) as the estimate reads them — position, direction and power after
+ * cyPhotonMap's quantisation (src/ext/cyPhotonMap.h:166-206) and ScalePhotonPowers — in emission order. Host arrays of
+ * 3 * capacity floats each (any may be NULL); *count = photons in the map. */
+int qg_photon_map_read(qgScene *scene, int32_t which, float *pos3, float *dir3, float *power3, size_t capacity, size_t *count);
+/* The body of the emission loop for emissions [first, first + n) of map `which`, without the map-full stop: counts[e] photons
+ * (at most bounce each) in records[(e * bounce + k) * 9] = position, incoming direction, power BEFORE the normalisation. */
+int qg_photon_emit(qgScene *scene, const qgPhotonParams *params, int32_t which, uint32_t first, size_t n, int32_t *counts, float *records);
+/* cyPhotonMap::EstimateIrradiance<100>(I, D, radius, pos, &normal, 1, FILTER_TYPE_QUADRATIC) (cyPhotonMap.h:333-395) at n points */
+int qg_photon_estimate(qgScene *scene, int32_t which, const float *pos3, const float *normal3, size_t n, float *irrad3, float *dir3);
+/* replaces map `which` by caller-supplied photons: AddPhoton (position, direction, power; quantised as cyPhotonMap does) and
+ * ScalePhotonPowers(power_scale) — lets a binding or a test hand over a map built elsewhere */
+int qg_photon_map_set(qgScene *scene, int32_t which, const float *pos3, const float *dir3, const float *power3, size_t n, float radius,
+                      float power_scale);
 
 /* ---- multi-GPU: the reference's rank model (Renderer_MPI, src/renderers/Renderer_MPI.cpp) over NCCL ----------------------
  * Every rank accumulates its shard of the frame — tiles k = r_t (mod G_t) of the reference's interleaved 4x4-tile rule

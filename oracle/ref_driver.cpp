@@ -341,6 +341,117 @@ void qaref_samples(int64_t n, const int32_t *pix, uint32_t seed, float *rgb, flo
   }
 }
 
+
+// ---- photon / caustics maps (the reference's -use-photon-map path) ------------------------------------------------------------
+// The body of the emission loops of Renderer::ComputeScene (renderer.cpp:143-196 photon map, :214-266 caustics map) for
+// emissions [first, first + n), each fed with the counter-based stream of (emission, map, seed) (P4 patch) and without the
+// map-full stop: counts[e] photons, rec[(e * bounceMax + k) * 9] = position, incoming direction, power before normalisation.
+int qaref_emit_photons(int which, uint32_t first, int64_t n, uint32_t seed, int bounceMax, int32_t *counts, float *rec)
+{
+  std::vector<Light *> photonLights;
+  for (auto light : scene.lights) {
+    if (light->IsPhotonSource()) { photonLights.push_back(light); }
+  }
+  if (photonLights.empty()) return 0;
+  const qaFLOAT lightScale = 1.f / static_cast<qaFLOAT>(photonLights.size());
+  for (int64_t e = 0; e < n; ++e) {
+    qaref_seed_path(qaref_path_key(first + (uint32_t) e, 0x50484F54u + (uint32_t) which, seed));
+    Light *light;
+    if (photonLights.size() == 1) { light = photonLights[0]; }
+    else {
+      qaFLOAT r;
+      rng->local().Get1f(r);
+      size_t id = which == 0 ? (size_t) MIN(FLOOR(r * photonLights.size()), photonLights.size() - 1)
+                             : MIN(static_cast<size_t>(CEIL(r * photonLights.size())), photonLights.size() - 1);
+      light = photonLights[id];
+    }
+    DiffRay ray = light->RandomPhoton();
+    ray.Normalize();
+    DiffHitInfo hInfo;
+    hInfo.Init();
+    Color3f intensity = light->GetPhotonIntensity(ray.c.dir) * lightScale;
+    size_t bounce = 0;
+    int cnt = 0;
+    while (bounce < (size_t) bounceMax) {
+      if (scene.TraceNodeNormal(scene.rootNode, ray, hInfo)) {
+        const Material *mtl = hInfo.c.node->GetMaterial();
+        if (!mtl) break;
+        if (mtl->IsPhotonSurface(0) && bounce != 0 && (which == 0 || !hInfo.c.hasDiffuseHit) && cnt < bounceMax) {
+          float *o = rec + ((size_t) e * bounceMax + cnt) * 9;
+          o[0] = hInfo.c.p.x; o[1] = hInfo.c.p.y; o[2] = hInfo.c.p.z;
+          o[3] = ray.c.dir.x; o[4] = ray.c.dir.y; o[5] = ray.c.dir.z;
+          o[6] = intensity.r; o[7] = intensity.g; o[8] = intensity.b;
+          ++cnt;
+        }
+        if (mtl->RandomPhotonBounce(ray, intensity, hInfo)) {
+          bool diffuseHit = hInfo.c.hasDiffuseHit;
+          ++bounce;
+          ray.Normalize();
+          hInfo.Init();
+          if (which == 1) hInfo.c.hasDiffuseHit = (diffuseHit || mtl->IsPhotonSurface(0));
+        } else { break; }
+      } else { break; }
+    }
+    counts[e] = cnt;
+  }
+  return 1;
+}
+
+// cyPhotonMap itself: a map built from the given photons (AddPhoton quantises them, ScalePhotonPowers, the balanced kd-tree of
+// PrepareForIrradianceEstimation) queried with EstimateIrradiance<100>(..., FILTER_TYPE_QUADRATIC) as Shade does
+// (MtlBlinn_PhotonMap.cpp:430-433). Also returns the photons as the map hands them back (GetPower / GetDirection).
+void qaref_photon_estimate(int64_t np, const float *pos, const float *dir, const float *power, float scale, float radius, int64_t nq,
+                           const float *qpos, const float *qnrm, float *irrad, float *dout, float *back_dir, float *back_power)
+{
+  cyPhotonMap map;
+  map.AllocatePhotons((unsigned) np);
+  for (int64_t i = 0; i < np; ++i)
+    map.AddPhoton(Point3(pos[3 * i], pos[3 * i + 1], pos[3 * i + 2]), Point3(dir[3 * i], dir[3 * i + 1], dir[3 * i + 2]),
+                  Color3f(power[3 * i], power[3 * i + 1], power[3 * i + 2]));
+  map.ScalePhotonPowers(scale);
+  for (int64_t i = 0; i < np && back_dir && back_power; ++i) {  // before the kd-tree reorders them
+    Point3 d;
+    Color3f c;
+    map[(unsigned) i].GetDirection(d);
+    map[(unsigned) i].GetPower(c);
+    back_dir[3 * i] = d.x; back_dir[3 * i + 1] = d.y; back_dir[3 * i + 2] = d.z;
+    back_power[3 * i] = c.r; back_power[3 * i + 1] = c.g; back_power[3 * i + 2] = c.b;
+  }
+  map.PrepareForIrradianceEstimation();
+  for (int64_t q = 0; q < nq; ++q) {
+    Color3f I;
+    Point3 D;
+    const Point3 N(qnrm[3 * q], qnrm[3 * q + 1], qnrm[3 * q + 2]);
+    map.EstimateIrradiance<100>(I, D, radius, Point3(qpos[3 * q], qpos[3 * q + 1], qpos[3 * q + 2]), &N, 1.f, cyPhotonMap::FILTER_TYPE_QUADRATIC);
+    irrad[3 * q] = I.r; irrad[3 * q + 1] = I.g; irrad[3 * q + 2] = I.b;
+    dout[3 * q] = D.x; dout[3 * q + 1] = D.y; dout[3 * q + 2] = D.z;
+  }
+}
+
+// RendererParam's photon switches (src/main.cpp:35-40); takes effect at the next qaref_load (ComputeScene builds the maps)
+void qaref_set_photon(int use, int photonMapSize, int causticsMapSize)
+{
+  g_param.SetPhotonMappingFlag(use != 0);
+  if (photonMapSize > 0) g_param.SetPhotonMapSize((size_t) photonMapSize);
+  if (causticsMapSize > 0) g_param.SetCausticsMapSize((size_t) causticsMapSize);
+}
+// the maps ComputeScene built, as the estimate reads them: n photons -> pos, dir, power (each 3n floats); returns the count
+int64_t qaref_photon_map(int which, int64_t cap, float *pos, float *dir, float *power)
+{
+  cyPhotonMap &m = which == 0 ? scene.photonmap.map : scene.causticsmap.map;
+  const int64_t n = (int64_t) m.NumPhotons();
+  for (int64_t i = 0; i < n && i < cap; ++i) {
+    Point3 d;
+    Color3f c;
+    m[(unsigned) i].GetDirection(d);
+    m[(unsigned) i].GetPower(c);
+    pos[3 * i] = m[(unsigned) i].position.x; pos[3 * i + 1] = m[(unsigned) i].position.y; pos[3 * i + 2] = m[(unsigned) i].position.z;
+    dir[3 * i] = d.x; dir[3 * i + 1] = d.y; dir[3 * i + 2] = d.z;
+    power[3 * i] = c.r; power[3 * i + 1] = c.g; power[3 * i + 2] = c.b;
+  }
+  return n;
+}
+
 // Serial fp32 render in the reference's own pixel order (tiles of 4x4 in k order, pixels in idx order,
 // renderer.cpp:387-403) with the reference's running mean (scene.cpp:113-121); fixed spp.
 // rgb: W*H*3 linear means. Used to pin the restatement bit-for-bit (same seed, same draw order).

@@ -72,7 +72,20 @@ class SceneDesc(C.Structure):
 class RenderParams(C.Structure):
     _fields_ = [("spp", i32), ("max_bounce", i32), ("srgb", i32), ("seed", u32), ("width", i32), ("height", i32),
                 ("tile_rank", i32), ("tile_ranks", i32), ("sample_begin", i32), ("sample_end", i32), ("batch_paths", i32),
-                ("sort_by_material", i32), ("material_class", i32), ("spp_min", i32)]
+                ("sort_by_material", i32), ("material_class", i32), ("spp_min", i32), ("use_photon_map", i32)]
+
+
+class PhotonParams(C.Structure):
+    _fields_ = [("photon_map_size", i32), ("photon_map_bounce", i32), ("photon_map_radius", f32), ("caustics_map_size", i32),
+                ("caustics_map_bounce", i32), ("caustics_map_radius", f32), ("seed", u32)]
+
+    @classmethod
+    def defaults(cls, seed=0x5EED):  # RendererParam (src/renderers/renderer.h:52-57)
+        return cls(10000, 20, 0.2, 1000, 20, 1.0, seed)
+
+
+class PhotonStats(C.Structure):
+    _fields_ = [("photons", u64 * 2), ("emitted", u64 * 2), ("emissions", u64 * 2), ("rays", u64 * 2), ("device_ms", C.c_double)]
 
 
 class RenderStats(C.Structure):
@@ -119,6 +132,12 @@ PROTOTYPES = {
     "qg_render_accumulate": (C.c_int, [vp, C.POINTER(RenderParams), vp, vp, vp, C.POINTER(RenderStats)]),
     "qg_resolve": (C.c_int, [vp, C.POINTER(RenderParams), vp, vp, vp, vp, vp, vp, vp, vp]),
     "qg_shard_coverage": (C.c_int, [C.POINTER(Camera), C.POINTER(RenderParams), vp]),
+    "qg_photon_maps_build": (C.c_int, [vp, C.POINTER(PhotonParams), C.POINTER(PhotonStats)]),
+    "qg_photon_maps_clear": (None, [vp]),
+    "qg_photon_map_read": (C.c_int, [vp, i32, vp, vp, vp, C.c_size_t, C.POINTER(C.c_size_t)]),
+    "qg_photon_emit": (C.c_int, [vp, C.POINTER(PhotonParams), i32, u32, C.c_size_t, vp, vp]),
+    "qg_photon_estimate": (C.c_int, [vp, i32, vp, vp, C.c_size_t, vp, vp]),
+    "qg_photon_map_set": (C.c_int, [vp, i32, vp, vp, vp, C.c_size_t, f32, f32]),
     "qg_shard_size": (C.c_int, [C.POINTER(Camera), C.POINTER(RenderParams), C.POINTER(u64), C.POINTER(u64), C.POINTER(u64)]),
     "qg_save_png_rgb8": (C.c_int, [C.c_char_p, vp, i32, i32]),
     "qg_save_png_depth": (C.c_int, [C.c_char_p, vp, i32, i32]),

@@ -82,6 +82,17 @@ struct DevBuf {
 
 }  // namespace
 
+// one photon map of a scene: the photons in emission order as cyPhotonMap would return them (GetPower / GetDirection), and
+// their grid-sorted copy on the device (api_photon.inc)
+struct PhotonMapStore {
+  std::vector<float> pos, dir, power;  // 3, 3, 1 per photon; power = Photon::power (the largest channel)
+  std::vector<uint32_t> color;         // Color24: r | g << 8 | b << 16
+  float radius = 0.f;
+  DevBuf<float4> pa, pb;
+  DevBuf<uint32_t> cells;
+  DPhotonMap dev{};
+};
+
 struct qgScene {
   int device = 0;  // every entry point that takes the scene makes this the calling thread's current device
   FlatScene flat;
@@ -106,6 +117,9 @@ struct qgScene {
   // frame-sized device planes of qg_render / qg_resolve, kept between calls
   DevBuf<float> fr_acc, fr_dep, rs_mean, rs_dep;
   DevBuf<uint8_t> rs_rgb8, rs_sc, rs_mask;
+  PhotonMapStore pm[2];  // [0] Scene::photonmap, [1] Scene::causticsmap (src/scene/scene.h:65-66)
+  bool pm_built = false;
+  bool want_gather = false;  // the next ensure_wf also allocates the gather-request queue
   int dev_num_area = 0;  // PointLight / SpotLight with size > 0.01 (lights.cpp:52,87)
   DevBuf<unsigned long long> stats;
   cudaStream_t stream = nullptr;
@@ -407,7 +421,8 @@ namespace {
 
 int ensure_wf(qgScene *sc, uint32_t capacity, bool carry_diff = false)
 {
-  if (sc->wf_capacity == capacity && (!carry_diff || sc->wf.h4 != nullptr)) return QG_OK;
+  if (sc->wf_capacity == capacity && (!carry_diff || sc->wf.h4 != nullptr) && (!sc->want_gather || sc->wf.g0 != nullptr)) return QG_OK;
+  carry_diff = carry_diff || sc->wf.h4 != nullptr;  // keep what an earlier render asked for
   for (void *p : sc->wf_allocs) cudaFree(p);
   sc->wf_allocs.clear();
   sc->wf_capacity = 0;
@@ -440,6 +455,13 @@ int ensure_wf(qgScene *sc, uint32_t capacity, bool carry_diff = false)
       CU(alloc4(&B.ps6[k], capacity));
     }
     CU(alloc4(&B.h4, capacity));
+  }
+  if (sc->want_gather) {  // photon-map gather requests: at most one per shaded hit
+    CU(alloc4(&B.g0, capacity));
+    CU(alloc4(&B.g1, capacity));
+    CU(alloc4(&B.g2, capacity));
+    CU(alloc4(&B.g3, capacity));
+    CU(alloc4(&B.g4, capacity));
   }
   CU(alloc4(&B.s0, shadow_cap));
   CU(alloc4(&B.s1, shadow_cap));
@@ -547,6 +569,14 @@ int make_params(const qgScene *sc, const qgRenderParams *rp, WfParams *P, Shard 
   P->carry_diff = class_carries_diff(rp->material_class) ? 1 : 0;
   // the constructors of MtlBlinn_Basic / MtlPhong_Basic switch the lights' inverse-square falloff off for the whole
   // process (MtlBlinn_Basic.cpp:18, lights.cpp:18-30); it happens as soon as the scene file declares one material
+  if (rp->use_photon_map) {
+    if (rp->material_class != QG_CLASS_PHOTONMAP) return fail(QG_EINVAL, "use_photon_map needs material_class 0 (MtlBlinn_PhotonMap)");
+    if (!sc->pm_built) return fail(QG_EINVAL, "use_photon_map without maps: call qg_photon_maps_build first (Renderer::ComputeScene)");
+    if ((unsigned long long) W * (unsigned long long) H >= (1ull << 30)) return fail(QG_EINVAL, "frame too large for the gather queue's slot field");
+    P->use_photon_map = 1;
+    P->pm[0] = sc->pm[0].dev;
+    P->pm[1] = sc->pm[1].dev;
+  }
   P->no_falloff = (rp->material_class == QG_CLASS_BLINN_BASIC || rp->material_class == QG_CLASS_PHONG_BASIC) && !sc->flat.materials.empty();
   return QG_OK;
 }
@@ -643,8 +673,12 @@ void run_wave(qgScene *sc, WfParams P, cudaStream_t st, uint64_t *launches, Kern
       *launches += 3;
     }
     launch_wf_shade(sc->dev, B, P, gs, st);
-    if (clk) clk->stamp(1, st);
     *launches += 1;
+    if (P.use_photon_map) {
+      launch_photon_gather(sc->dev, B, P, st);
+      *launches += 1;
+    }
+    if (clk) clk->stamp(1, st);
     if (any_shadow && st2 != st) cudaEventRecord(sc->ev_shade, st);
   };
   auto trace = [&](int d) {
@@ -711,6 +745,7 @@ int render_accumulate(qgScene *sc, const qgRenderParams *rp, float *d_accum, flo
   if ((unsigned long long) wave > sh.total_paths) wave = (uint32_t) std::max<unsigned long long>(32ull, (sh.total_paths + 31ull) & ~31ull);
   if ((unsigned long long) wave * growth > (1ull << 31)) return fail(QG_EINVAL, "max_bounce too deep for this material class");
   cap = (uint32_t) ((unsigned long long) wave * growth);
+  sc->want_gather = sc->want_gather || P.use_photon_map != 0;
   rc = ensure_wf(sc, cap, P.carry_diff != 0);
   if (rc) return rc;
   P.accum = d_accum;
@@ -822,6 +857,7 @@ int render_adaptive(qgScene *sc, const qgRenderParams *rp, float *d_accum, float
     CU(cudaMemsetAsync(d_rad.p, 0, 4 * np * sizeof(float), st));
     uint32_t wave = (uint32_t) std::min<unsigned long long>(np, round_cap);
     wave = (wave + 31u) & ~31u;
+    sc->want_gather = sc->want_gather || P.use_photon_map != 0;
     rc = ensure_wf(sc, (uint32_t) ((unsigned long long) wave * growth), P.carry_diff != 0);
     if (rc) return rc;
     for (size_t base = 0; base < np; base += wave) {
@@ -890,3 +926,4 @@ int resolve_to_host(qgScene *sc, int W, int H, int spp, int srgb, const float *d
 
 #include "api_entry.inc"  // the extern "C" entry points
 #include "api_multi.inc"  // ... and the multi-GPU ones (NCCL)
+#include "api_photon.inc"  // ... and the photon / caustics maps

@@ -189,8 +189,8 @@ __device__ __forceinline__ void traverse_block(const DScene &S, IO &io, uint32_t
       float z = 0.f, mesh_exit = 0.f;
       uint32_t cur = QB_REF_EMPTY, flags = 0u;
       int sp = 0;
-#pragma unroll 1
       bool done = false;  // this lane's ray has left the phase (a leaf, or its mesh is finished): handed on at the next refill
+#pragma unroll 1
       for (int rep = 0; rep < QB_BP_INNER_REPS; ++rep) {
         // Hand-over and refill are batched: with a lane or two at a time they cost as many issue slots as a node visit
         // (ncu: 20 % of the kernel's instructions at 5-7 of 32 lanes). Lanes whose ray has left wait until QB_BP_REFILL

@@ -15,14 +15,15 @@
 
 namespace qaray_b200 {
 
-// RendererParam (renderer.h:47-68). The photon-map switches are accepted and refused at Render time: the photon
-// pass is outside this path ("next" row 3).
+// RendererParam (renderer.h:47-68), photon-map switches included: ComputeScene builds the maps (renderer.cpp:118-291).
 struct RendererParam {
   bool useSRGB = true;
   size_t sppMax = 8;
   size_t sppMin = 4;
   bool usePhotonMap = false;
   size_t photonMapSize = 10000, causticsMapSize = 1000;
+  size_t photonMapBounce = 20, causticsMapBounce = 20;
+  float photonMapRadius = 0.2f, causticsMapRadius = 1.0f;
   int maxBounce = 5;  // Material::maxBounce (src/core/material.cpp:31)
   unsigned seed = 0x5EEDu;
   int width = 0, height = 0;  // 0 = the XML camera's
@@ -52,6 +53,8 @@ class Renderer_B200 {
   std::vector<uint8_t> colorBuffer, sampleCountBuffer, maskBuffer;  // FrameBuffer planes (src/fb/framebuffer.h:35-95)
   std::vector<float> depthBuffer, linearBuffer;
   qgRenderStats stats{};
+  qgPhotonStats photonStats{};
+  bool mapsBuilt = false;
 
   explicit Renderer_B200(RendererParam &p) : param(p) {}
   ~Renderer_B200() { Terminate(); }
@@ -105,12 +108,28 @@ class Renderer_B200 {
     sampleCountBuffer.assign(n, 0);
     maskBuffer.assign(n, 0);
     linearBuffer.assign(3 * n, 0.f);
+    // Initialize Photon Map (renderer.cpp:115-291); "TODO: Photon Map for MPI Mode" there: single-GPU here as well
+    if (param.usePhotonMap && param.photonMapSize > 0 && param.causticsMapSize > 0) {
+      if (multi) { fprintf(stderr, "Renderer_B200: -use-photon-map and -gpus do not combine\n"); return false; }
+      qgPhotonParams pp{};
+      pp.photon_map_size = (int32_t) param.photonMapSize; pp.photon_map_bounce = (int32_t) param.photonMapBounce;
+      pp.photon_map_radius = param.photonMapRadius;
+      pp.caustics_map_size = (int32_t) param.causticsMapSize; pp.caustics_map_bounce = (int32_t) param.causticsMapBounce;
+      pp.caustics_map_radius = param.causticsMapRadius;
+      pp.seed = param.seed;
+      if (qg_photon_maps_build(scene, &pp, &photonStats) != QG_OK) {
+        fprintf(stderr, "Renderer_B200::ComputeScene: %s\n", qg_last_error());
+        return false;
+      }
+      printf("\nPhoton Map: %llu photons, Caustics Map: %llu photons, %.3f ms\n", (unsigned long long) photonStats.photons[0],
+             (unsigned long long) photonStats.photons[1], photonStats.device_ms);
+      mapsBuilt = true;
+    }
     return true;
   }
   // Renderer::Render (batch): ThreadRender over this shard's tiles; fills the planes PixelRender fills
   bool Render()
   {
-    if (param.usePhotonMap) { fprintf(stderr, "Renderer_B200: -use-photon-map is not on the GPU path\n"); return false; }
     qgRenderParams rp{};
     rp.spp = (int32_t) param.sppMax;
     rp.max_bounce = param.maxBounce;
@@ -123,6 +142,7 @@ class Renderer_B200 {
     rp.material_class = param.materialClass;
     rp.sort_by_material = param.sortByMaterial ? 1 : 0;
     rp.spp_min = param.sppMin < param.sppMax ? (int32_t) param.sppMin : 0;  // SuperSamplerHalton's adaptive stop
+    rp.use_photon_map = mapsBuilt ? 1 : 0;  // scene->usePhotonMap = param.usePhotonMap (renderer.cpp:117)
     if (multi) {
       if (mpiSize > 1) { fprintf(stderr, "Renderer_B200: -shard and -gpus do not combine\n"); return false; }
       rp.tile_rank = 0;

@@ -279,6 +279,7 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade(const DScene S, const WfB
     // next path
     V3 next_dir = v3(0.f), next_T = v3(0.f), next_absorb = v3(0.f);
     uint32_t next_flags = 0;
+    uint32_t gather = 0u;  // photon-map gathers this hit asks for (bit 30 photon map, bit 31 caustics map)
     Rng rng = {0u, 0u};
 
     if (idx < n) {
@@ -379,6 +380,9 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade(const DScene S, const WfB
           else if (select < coefR && lumaR > color_luma_threshold) sel = SEL_REFLECT;
           else if (select < coefD && lumaD > color_luma_threshold) sel = SEL_DIFFUSE;
           else sel = SEL_ABSORB;
+          // Scene::usePhotonMap (:341-352): a diffuse pick gathers the caustics map, and the photon map instead of a further
+          // diffuse bounce once the path has had one; the bounce rule below is the same with and without the maps
+          if (P.use_photon_map && sel == SEL_DIFFUSE) gather = 0x80000000u | ((flags & QB_FLAG_DIFFUSE_HIT) ? 0x40000000u : 0u);
           if (bounce_count > 0) {
             if (sel == SEL_REFLECT) {  // SampleReflectionBxDF (:179-203)
               V3 dir = rDir;
@@ -457,6 +461,24 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade(const DScene S, const WfB
       }
     }
 
+    // ---- photon-map gathers (:426-458) are queued for k_photon_gather: the k-nearest search keeps 100 candidates per thread
+    if (P.use_photon_map) {
+      const uint32_t gm = __ballot_sync(0xFFFFFFFFu, gather != 0u);
+      if (gm) {
+        uint32_t gb = 0;
+        if (lane == 0) gb = atomicAdd(&B.counters[QB_CNT_GATHER + d], (uint32_t) __popc(gm));
+        gb = __shfl_sync(0xFFFFFFFFu, gb, 0);
+        const uint32_t q = gb + (uint32_t) __popc(gm & lt_mask);
+        if (gather && q < B.capacity) {
+          B.g0[q] = make_float4(p.x, p.y, p.z, N.x);
+          B.g1[q] = make_float4(N.y, N.z, V.x, V.y);
+          B.g2[q] = make_float4(V.z, Kd.x, Kd.y, Kd.z);
+          B.g3[q] = make_float4(Ks.x, Ks.y, Ks.z, gloss);
+          B.g4[q] = make_float4(T.x, T.y, T.z, __uint_as_float((uint32_t) slot | gather));
+        }
+      }
+    }
+
     // ---- queue compaction: surviving paths go to the state buffer of depth d+1
     const uint32_t amask = __ballot_sync(0xFFFFFFFFu, alive);
     if (amask) {
@@ -475,6 +497,7 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade(const DScene S, const WfB
 
 }  // namespace qb
 #include "shade_alt.cuh"
+#include "photon.cuh"
 namespace qb {
 
 // ---- resolve ---------------------------------------------------------------------------------------------------------

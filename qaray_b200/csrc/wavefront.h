@@ -36,7 +36,8 @@ namespace qb {
 #define QB_CNT_FETCH_REDO 128  // [128 .. 143] work-fetch cursor of k_redo_exact
 #define QB_CNT_HOLES_PATHS 144  // [144 .. 159] dead entries in the path queue of depth d (unused tails of the shade warps' reservations)
 #define QB_CNT_HOLES_SHADOW 160 // [160 .. 175] dead entries in the shadow queue of depth d
-#define QB_CNT_WORDS 176
+#define QB_CNT_GATHER 176      // [176 .. 191] photon-map gather requests queued by shade(d) (-use-photon-map)
+#define QB_CNT_WORDS 192
 
 // area lights (PointLight / SpotLight with size > 0.01, src/lights/lights.cpp:50-65,84-101): shadow samples per group
 #ifndef QB_SHADE_CHUNK
@@ -48,6 +49,20 @@ namespace qb {
 #define QB_MAT_BINS 256        // material sort: bin 0 = miss, 1 = no material / MultiMtl out of range, 2 + i = material i
 #define QB_AREA_SPP_MIN 16     // GenLight::shadow_spp_min (lights.cpp:16)
 #define QB_AREA_SPP_MAX 64     // GenLight::shadow_spp_max (lights.cpp:17)
+
+// Photon map as the gather kernel reads it (photon.cuh): photons sorted by the cell of a uniform grid over their bounds
+// (cell edge >= the gather radius, so a query looks at 3 x 3 x 3 cells), dequantised the way cyPhotonMap::Photon::GetPower /
+// GetDirection return them (src/ext/cyPhotonMap.h:61-70,186-206).
+struct DPhotonMap {
+  const float4 *pa;            // position.xyz, max power (Photon::power after ScalePhotonPowers)
+  const float4 *pb;            // direction.xyz, colour bits (r | g << 8 | b << 16 of the Color24)
+  const uint32_t *cell_start;  // dims.x * dims.y * dims.z + 1 offsets
+  float origin[3];
+  float inv_cell;
+  int32_t dims[3];
+  uint32_t count;
+  float radius;                // PhotonMap::radius of the scene (renderer.cpp:123-127)
+};
 
 struct WfBuffers {
   // path state, ping-pong by depth parity: [d & 1]
@@ -79,6 +94,12 @@ struct WfBuffers {
   // deferred checks of the degenerate-axis cull (traverse.cuh): {ray index, object, z at mesh entry (bits), flag}
   uint4 *redo;
   uint32_t redo_capacity;
+  // photon-map gather requests of the depth being shaded (allocated by the first render with use_photon_map)
+  float4 *g0;  // p.xyz, N.x
+  float4 *g1;  // N.yz, V.xy
+  float4 *g2;  // V.z, diffuse.rgb
+  float4 *g3;  // specular.rgb, glossiness
+  float4 *g4;  // throughput.rgb, accum slot | maps << 30 (bit 30 photon map, bit 31 caustics map)
   // material sort of the shade queue (optional): permutation and the per-material bins / offsets
   uint32_t *perm;      // capacity entries
   uint32_t *mat_bins;  // 2 * QB_MAT_BINS: counts, then running offsets
@@ -86,6 +107,20 @@ struct WfBuffers {
   unsigned long long *stats;  // [0] closest rays, [1] shadow rays, [2] nodes, [3] tris, [4] objects
   uint32_t capacity;          // paths per wave
   uint32_t shadow_capacity;   // capacity * number of non-ambient lights
+};
+
+// A batch of emissions [e0, e0 + E). rays / path_of are compact ping-pong arrays of the photons still flying; everything else
+// is indexed by the emission's position in the batch.
+struct PhotonBatch {
+  qgRay *rays[2];
+  uint32_t *path_of[2];
+  qgHit *hits;          // closest hits of rays[cur] (launch_trace_closest_rays)
+  float4 *state;        // photon power r g b, packed: bounce | hasDiffuseHit << 8
+  uint32_t *rng_n;      // draws consumed from the emission's stream
+  uint32_t *count;      // photons recorded by the emission
+  float *rec;           // [emission][max_bounce][9]: position, incoming direction, power
+  uint32_t *n_next;     // survivors appended to rays[cur ^ 1]
+  int32_t max_bounce;
 };
 
 struct WfParams {
@@ -110,6 +145,8 @@ struct WfParams {
   int32_t mtl_class;         // QG_CLASS_*: which of the reference's MtlBlinn classes shades (materials.h:57-61)
   int32_t carry_diff;        // secondary paths carry differential rays (ps4..ps6 / h4 allocated)
   int32_t no_falloff;        // DisableInverseSquareFalloff() was called (MtlBlinn_Basic.cpp:18, lights.cpp:21-30)
+  int32_t use_photon_map;    // Scene::usePhotonMap: diffuse hits gather from pm[0] (photon map) / pm[1] (caustics map)
+  DPhotonMap pm[2];
   float *accum;              // float4 per slot: sum r,g,b, weight
   float *depth_plane;        // may be null
 };
@@ -176,6 +213,11 @@ void launch_wf_shade(const DScene &S, const WfBuffers &B, const WfParams &P, int
 void launch_wf_area(const DScene &S, const WfBuffers &B, const WfParams &P, int grid, cudaStream_t st);  // area shadow rays + resolve
 void launch_mat_sort(const DScene &S, const WfBuffers &B, const WfParams &P, cudaStream_t st);  // builds B.perm for shade(P.depth)
 void launch_wf_stats(const WfBuffers &B, int max_bounce, cudaStream_t st);
+void launch_photon_gather(const DScene &S, const WfBuffers &B, const WfParams &P, cudaStream_t st);  // the gather requests of shade(P.depth)
+void launch_photon_emit(const DScene &S, const PhotonBatch &Bt, uint32_t e0, uint32_t E, int map, uint32_t seed, int n_plights, const int32_t *plights,
+                        cudaStream_t st);
+void launch_photon_step(const DScene &S, const PhotonBatch &Bt, int cur, uint32_t n_cur, int map, uint32_t e0, uint32_t seed, cudaStream_t st);
+void launch_photon_estimate(const DPhotonMap &M, const float *pos, const float *nrm, uint32_t n, float *irrad, float *dir, cudaStream_t st);
 // adaptive sampling (SuperSamplerHalton, src/scene/scene.cpp:83-123), see shade_kernels.cu
 void launch_adaptive_build(int W, int H, int tile_rank, int tile_ranks, const int32_t *count, const uint8_t *active, int chunk,
                            uint32_t *n_active, int32_t *list, int32_t *triples, cudaStream_t st);

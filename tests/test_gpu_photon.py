@@ -1,0 +1,189 @@
+"""GPU tests of the photon / caustics maps (`-use-photon-map`) through the C ABI, stage by stage against
+tests/golden/photon_<scene>.npz (tools/make_photon_golden.py, the reference itself):
+
+  emission   qg_photon_emit = the body of the emission loops (src/renderers/renderer.cpp:143-196, :214-266) for emissions
+             0..4095, same counter-based stream per emission as the oracle: photon counts, positions, directions, powers
+  quantise   qg_photon_map_set / qg_photon_map_read = AddPhoton + ScalePhotonPowers + GetDirection / GetPower
+             (src/ext/cyPhotonMap.h:166-206): bit-equal
+  estimate   qg_photon_estimate = EstimateIrradiance<100> with the quadratic filter (cyPhotonMap.h:333-495), the reference's
+             kd-tree against the uniform grid here
+  build      qg_photon_maps_build: the stopping rule and the power normalisation (renderer.cpp:143-199)
+  image      a render with use_photon_map against the reference's two renders of the same scene (its own emission pass and
+             random streams): as close to run A as run B is, on tone-compressed radiance (the estimator is heavy-tailed)
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from conftest import ASSETS, GOLDEN_DIR, ROOT, scene_xml
+from qaray_b200 import capi
+
+pytestmark = pytest.mark.gpu
+
+
+def names():
+    if not os.path.isdir(GOLDEN_DIR):
+        return []
+    return sorted(f[7:-4] for f in os.listdir(GOLDEN_DIR) if f.startswith("photon_") and f.endswith(".npz"))
+
+
+def cases():
+    out = []
+    for n in names():
+        g = np.load(os.path.join(GOLDEN_DIR, "photon_%s.npz" % n))
+        out += [(n, w) for w in (0, 1) if "photons%d" % w in g.files]
+    return out
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def open_scene(name):
+    lib = capi.load()
+    capi.check(lib, lib.qg_init(0))
+    h = C.c_void_p()
+    capi.check(lib, lib.qg_scene_load_xml(os.fsencode(scene_xml(name)), os.fsencode(ASSETS), C.byref(h)))
+    return lib, h
+
+
+@pytest.mark.parametrize("name,which", cases())
+def test_emission_matches_reference(name, which):
+    g = np.load(os.path.join(GOLDEN_DIR, "photon_%s.npz" % name))
+    ref_counts, ref_ph, bounce = g["counts%d" % which], g["photons%d" % which], int(g["bounce"])
+    n = len(ref_counts)
+    lib, h = open_scene(name)
+    pp = capi.PhotonParams.defaults(int(g["seed"]))
+    pp.photon_map_bounce = pp.caustics_map_bounce = bounce
+    counts = np.zeros(n, np.int32)
+    rec = np.zeros((n, bounce, 9), np.float32)
+    capi.check(lib, lib.qg_photon_emit(h, C.byref(pp), which, 0, n, _p(counts), _p(rec)))
+    lib.qg_scene_destroy(h)
+    same = counts == ref_counts
+    # libm differences (sinf / cosf / powf in the last ulp) may flip a lobe choice or a grazing hit now and then
+    assert same.mean() >= 0.995, "%d of %d emissions store a different number of photons" % ((~same).sum(), n)
+    off = np.concatenate([[0], np.cumsum(ref_counts)])
+    bad = 0
+    for e in np.nonzero(same & (ref_counts > 0))[0]:
+        a, b = rec[e, :counts[e]], ref_ph[off[e]:off[e + 1]]
+        ok = (np.abs(a[:, :6] - b[:, :6]) <= 2e-4 + 2e-4 * np.abs(b[:, :6])).all() and (np.abs(a[:, 6:] - b[:, 6:]) <= 1e-6 + 5e-4 * np.abs(b[:, 6:])).all()
+        bad += not ok
+    assert bad <= max(2, int(0.005 * n)), "%d emissions differ in position / direction / power" % bad
+
+
+@pytest.mark.parametrize("name,which", cases())
+def test_quantisation_and_estimate_match_cyphotonmap(name, which):
+    g = np.load(os.path.join(GOLDEN_DIR, "photon_%s.npz" % name))
+    ph, scale, radius = g["photons%d" % which], float(g["scale%d" % which]), float(g["radius%d" % which])
+    lib, h = open_scene(name)
+    pos, d, pw = (np.ascontiguousarray(ph[:, k:k + 3]) for k in (0, 3, 6))
+    capi.check(lib, lib.qg_photon_map_set(h, which, _p(pos), _p(d), _p(pw), len(ph), radius, scale))
+    bp, bd, bw = np.zeros_like(pos), np.zeros_like(pos), np.zeros_like(pos)
+    cnt = C.c_size_t()
+    capi.check(lib, lib.qg_photon_map_read(h, which, _p(bp), _p(bd), _p(bw), len(ph), C.byref(cnt)))
+    assert cnt.value == len(ph) and np.array_equal(bp, pos)
+    assert np.array_equal(bd, g["back_dir%d" % which]), "direction quantisation differs from cyPhotonMap's"
+    assert np.array_equal(bw, g["back_power%d" % which]), "power quantisation differs from cyPhotonMap's"
+    qpos, qn = np.ascontiguousarray(g["qpos%d" % which]), np.ascontiguousarray(g["qnrm%d" % which])
+    irrad, dout = np.zeros_like(qpos), np.zeros_like(qpos)
+    capi.check(lib, lib.qg_photon_estimate(h, which, _p(qpos), _p(qn), len(qpos), _p(irrad), _p(dout)))
+    lib.qg_scene_destroy(h)
+    ri, rd = g["irrad%d" % which], g["dir%d" % which]
+    # same 100 photons, summed in a different order; equal distances at the 100th place may pick a different photon
+    close = (np.abs(irrad - ri) <= 1e-6 + 2e-4 * np.abs(ri)).all(axis=1) & (np.abs(dout - rd) <= 2e-4).all(axis=1)
+    assert close.mean() >= 0.998, "%d of %d estimates differ" % ((~close).sum(), len(close))
+    assert ((irrad.sum(1) > 0) == (ri.sum(1) > 0)).mean() >= 0.999
+
+
+def test_build_fills_the_maps_by_the_reference_rule():
+    name = "trc_mtl_glass"
+    lib, h = open_scene(name)
+    pp = capi.PhotonParams.defaults(0x5EED)
+    pp.photon_map_size, pp.caustics_map_size = 5000, 300
+    st = capi.PhotonStats()
+    capi.check(lib, lib.qg_photon_maps_build(h, C.byref(pp), C.byref(st)))
+    assert (st.photons[0], st.photons[1]) == (5000, 300) and st.emitted[0] > 0 and st.emitted[1] > 0
+    assert st.rays[0] >= st.emissions[0] and st.device_ms > 0
+    for which, size in ((0, 5000), (1, 300)):
+        pos, d, pw = (np.zeros((size, 3), np.float32) for _ in range(3))
+        cnt = C.c_size_t()
+        capi.check(lib, lib.qg_photon_map_read(h, which, _p(pos), _p(d), _p(pw), size, C.byref(cnt)))
+        assert cnt.value == size
+        # the map = the photons of emissions 0, 1, 2, ... in that order until it is full (renderer.cpp:143-196) ...
+        ne = int(st.emissions[which])
+        counts = np.zeros(ne, np.int32)
+        rec = np.zeros((ne, 20, 9), np.float32)
+        capi.check(lib, lib.qg_photon_emit(h, C.byref(pp), which, 0, ne, _p(counts), _p(rec)))
+        flat = np.concatenate([rec[e, :counts[e]] for e in range(ne) if counts[e]], 0)
+        assert len(flat) >= size and np.array_equal(flat[:size, :3], pos)
+        # ... and numOfEmittedRays counts the emissions that stored at least one of them
+        first = np.concatenate([[0], np.cumsum(counts)])[:-1]
+        emitted = int(((counts > 0) & (first < size)).sum())
+        assert emitted == st.emitted[which]
+        # power = the largest channel / numOfEmittedRays, colour in 8 bits per channel
+        want = flat[:size, 6:].max(axis=1) * (np.float32(1.0) / np.float32(emitted))
+        assert np.allclose(pw.max(axis=1), want, rtol=4.1e-3)  # 255 * c / power may truncate to 254 for the largest channel itself
+    # deterministic: the same seed gives the same maps whatever the batch
+    pos2 = np.zeros((5000, 3), np.float32)
+    capi.check(lib, lib.qg_photon_maps_build(h, C.byref(pp), None))
+    capi.check(lib, lib.qg_photon_map_read(h, 0, _p(pos2), None, None, 5000, None))
+    capi.check(lib, lib.qg_photon_map_read(h, 0, _p(pos), None, None, 5000, None))
+    assert np.array_equal(pos, pos2)
+    lib.qg_photon_maps_clear(h)
+    rp = capi.RenderParams(1, 5, 1, 0x5EED, 32, 24, 0, 1, 0, 0, 0, 0, 0, 0, 1)
+    assert lib.qg_render(h, C.byref(rp), None, None, None, None, None, None) == capi.QG_EINVAL  # maps cleared: refuse loudly
+    lib.qg_scene_destroy(h)
+
+
+def test_scene_without_photon_source_or_unfillable_map():
+    lib, h = open_scene("example_project12_caustics_glossy")
+    pp = capi.PhotonParams.defaults()
+    pp.photon_map_size, pp.caustics_map_size = 500, 50
+    # every material of this scene has a diffuse colour: no photon arrives by a specular-only route, the caustics map can never
+    # fill (the reference's loop never ends on it); here the build reports it
+    assert lib.qg_photon_maps_build(h, C.byref(pp), None) == capi.QG_EINVAL
+    assert b"cannot be filled" in lib.qg_last_error()
+    lib.qg_scene_destroy(h)
+
+
+def test_render_with_photon_maps_matches_reference_statistically():
+    name = "trc_mtl_glass"
+    g = np.load(os.path.join(GOLDEN_DIR, "photon_%s.npz" % name))
+    W, H, spp = (int(v) for v in g["img_size"])
+    lib, h = open_scene(name)
+    pp = capi.PhotonParams.defaults(0x5EED)
+    pp.photon_map_size, pp.caustics_map_size = (int(v) for v in g["map_sizes"])
+    capi.check(lib, lib.qg_photon_maps_build(h, C.byref(pp), None))
+    lin = np.zeros((H, W, 3), np.float32)
+    st = capi.RenderStats()
+    rp = capi.RenderParams(spp, 5, 1, 0x5EED, W, H, 0, 1, 0, 0, 0, 0, 0, 0, 1)
+    capi.check(lib, lib.qg_render(h, C.byref(rp), _p(lin), None, None, None, None, C.byref(st)))
+    off = np.zeros((H, W, 3), np.float32)
+    rp0 = capi.RenderParams(spp, 5, 1, 0x5EED, W, H, 0, 1, 0, 0, 0, 0, 0, 0, 0)
+    capi.check(lib, lib.qg_render(h, C.byref(rp0), _p(off), None, None, None, None, None))
+    lib.qg_scene_destroy(h)
+    a, b = g["img_a"].astype(np.float64), g["img_b"].astype(np.float64)
+    t = lambda x: x / (1.0 + x)  # the gather divides photon powers by small pick probabilities: compare on a bounded scale
+    rm = lambda p, q: float(np.sqrt(((t(p) - t(q)) ** 2).mean()))
+    x = lin.astype(np.float64)
+    assert np.isfinite(x).all()
+    floor, err = rm(a, b), rm(x, a)
+    assert err <= 1.25 * floor, "tone-compressed RMSE %.4f against the reference's own %.4f" % (err, floor)
+    ma, mb, mx = t(a).mean(), t(b).mean(), t(x).mean()
+    assert abs(mx - 0.5 * (ma + mb)) <= 3.0 * abs(ma - mb) + 0.02, (mx, ma, mb)
+    assert t(x).mean() > t(off.astype(np.float64)).mean() + 0.05, "the maps add light: the render without them must be darker"
+
+
+def test_cli_accepts_use_photon_map(tmp_path):
+    cli = os.path.join(ROOT, "qaray_b200", "qaray_b200_cli")
+    if not os.path.exists(cli):
+        pytest.fail("qaray_b200_cli is missing: run __graft_entry__.build()")
+    r = subprocess.run([cli, "-batch", "-spp", "4", "-size", "64", "48", "-use-photon-map", "-photon-map-size", "2000", "-caustics-map-size", "100",
+                        "-assets", ASSETS, "-out", str(tmp_path) + os.sep, scene_xml("trc_mtl_glass")], stdout=subprocess.PIPE,
+                       stderr=subprocess.STDOUT, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout
+    assert "Photon Map: 2000 photons, Caustics Map: 100 photons" in r.stdout
+    assert os.path.exists(str(tmp_path / "colorBuffer.png"))

@@ -35,7 +35,8 @@ def test_struct_sizes_match_the_header():
     assert C.sizeof(capi.TexturedColor) == 100
     assert C.sizeof(capi.Light) == 52
     assert C.sizeof(capi.Camera) == 56
-    assert C.sizeof(capi.RenderParams) == 56
+    assert C.sizeof(capi.RenderParams) == 60
+    assert C.sizeof(capi.PhotonParams) == 28 and C.sizeof(capi.PhotonStats) == 72
     assert capi.RAY_DTYPE.itemsize == 76 and capi.HIT_DTYPE.itemsize == 88
 
 
