@@ -46,6 +46,7 @@
 #include "lights/lights.h"
 #include "materials/materials.h"
 #include "samplers/sampler_selection.h"
+#include "tiny_obj_loader.h"  // the reference's vendored tinyobjloader v1.1.0 (external/tinyobjloader), implementation in mesh/TriMesh.cpp
 
 #ifdef QAREF_COUNTERS
 // defined by the patched copy of scene/scene.cpp (see oracle/Makefile)
@@ -450,6 +451,42 @@ int64_t qaref_photon_map(int which, int64_t cap, float *pos, float *dir, float *
     power[3 * i] = c.r; power[3 * i + 1] = c.g; power[3 * i + 2] = c.b;
   }
   return n;
+}
+
+// tinyobjloader itself, as TriMesh::LoadFromFileObj calls it (src/mesh/TriMesh.cpp:63-100: triangulate = true): the attribute
+// arrays and, per triangle, 9 indices (v n t per corner) + the material id, in file order. For the parser fuzz test.
+// counts[5] = floats in vertices / normals / texcoords, triangles, materials. Returns 0 when LoadObj fails.
+int qaref_tinyobj_load(const char *obj_path, const char *mtl_dir, int64_t *counts, float *vertices, float *normals, float *texcoords,
+                       int32_t *tri10, int64_t cap_floats, int64_t cap_tris)
+{
+  tinyobj::attrib_t attrib;
+  std::vector<tinyobj::shape_t> shapes;
+  std::vector<tinyobj::material_t> materials;
+  std::string err;
+  if (!tinyobj::LoadObj(&attrib, &shapes, &materials, &err, obj_path, mtl_dir, true)) return 0;
+  counts[0] = (int64_t) attrib.vertices.size(); counts[1] = (int64_t) attrib.normals.size(); counts[2] = (int64_t) attrib.texcoords.size();
+  for (size_t i = 0; i < attrib.vertices.size() && (int64_t) i < cap_floats; ++i) vertices[i] = attrib.vertices[i];
+  for (size_t i = 0; i < attrib.normals.size() && (int64_t) i < cap_floats; ++i) normals[i] = attrib.normals[i];
+  for (size_t i = 0; i < attrib.texcoords.size() && (int64_t) i < cap_floats; ++i) texcoords[i] = attrib.texcoords[i];
+  int64_t nt = 0;
+  for (auto &sh : shapes) {
+    size_t off = 0;
+    for (size_t f = 0; f < sh.mesh.num_face_vertices.size(); ++f) {
+      const int fv = sh.mesh.num_face_vertices[f];
+      if (fv == 3 && nt < cap_tris) {
+        for (int k = 0; k < 3; ++k) {
+          const tinyobj::index_t &ix = sh.mesh.indices[off + k];
+          tri10[10 * nt + 3 * k + 0] = ix.vertex_index; tri10[10 * nt + 3 * k + 1] = ix.normal_index; tri10[10 * nt + 3 * k + 2] = ix.texcoord_index;
+        }
+        tri10[10 * nt + 9] = sh.mesh.material_ids[f];
+      }
+      if (fv == 3) ++nt;
+      off += fv;
+    }
+  }
+  counts[3] = nt;
+  counts[4] = (int64_t) materials.size();
+  return 1;
 }
 
 // Serial fp32 render in the reference's own pixel order (tiles of 4x4 in k order, pixels in idx order,
