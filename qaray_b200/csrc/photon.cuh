@@ -10,8 +10,8 @@
 // The reference emits photons one after another from one random stream until the map is full. Here emission e has its own
 // counter-based stream (key = rng_key(e, map, seed)), emissions are traced in batches through the ray-buffer kernels of
 // trace_kernels.cu, and the host keeps the photons of emissions 0, 1, 2, ... in that order until the map is full — the same
-// stopping rule, independent of batch size. The kd-tree of cyPhotonMap is replaced by a uniform grid: the estimate only
-// depends on WHICH photons are the 100 nearest, not on the structure that finds them.
+// stopping rule, independent of batch size. The estimate walks cyPhotonMap's own balanced kd-tree (built on the host,
+// api_photon.inc) in the reference's order, because its result is order-dependent (photon_estimate below).
 #pragma once
 
 namespace qb {
@@ -88,8 +88,24 @@ __device__ __forceinline__ void heap_offer(PhotonHeap &h, float dist2, uint32_t 
   }
 }
 
+// One photon of the tree against the query (the tail of LocatePhotons, cyPhotonMap.h:443-494)
+__device__ __forceinline__ void photon_visit(const DPhotonMap &M, uint32_t idx, V3 pos, V3 N, PhotonHeap &h)
+{
+  const float4 a4 = M.pa[idx];
+  const V3 dif = v3(a4.x, a4.y, a4.z) - pos;
+  const float dist2 = length2(dif);
+  if (dist2 < h.dist2[0]) {
+    const float4 b4 = M.pb[idx];
+    if (dot(v3(b4.x, b4.y, b4.z), N) >= 0) return;  // the photon arrived from behind the surface
+    heap_offer(h, dist2, idx);
+  }
+}
+
 // EstimateIrradiance<100>(I, D, radius, pos, &N, 1.f, FILTER_TYPE_QUADRATIC). Returns false when no photon was found
-// (I = 0, D = 0 then, as the reference leaves them).
+// (I = 0, D = 0 then, as the reference leaves them). LocatePhotons (:424-442) is a recursion — near child, far child if the
+// splitting plane is closer than the current search radius, then the node's own photon — replayed here with an explicit
+// stack in exactly that order: the 101st candidate replaces the heap's farthest photon even when it is farther itself
+// (heap_offer's else branch only ever compared it with the map's radius), so which photons survive depends on the order.
 __device__ __noinline__ bool photon_estimate(const DPhotonMap &M, V3 pos, V3 N, V3 &irrad, V3 &direction)
 {
   irrad = v3(0.f);
@@ -98,32 +114,32 @@ __device__ __noinline__ bool photon_estimate(const DPhotonMap &M, V3 pos, V3 N, 
   PhotonHeap h;
   h.found = 0;
   h.dist2[0] = M.radius * M.radius;
-  const float r = M.radius;
-  int lo[3], hi[3];
   const float q[3] = {pos.x, pos.y, pos.z};
-  for (int a = 0; a < 3; ++a) {
-    lo[a] = max(0, (int) floorf((q[a] - r - M.origin[a]) * M.inv_cell));
-    hi[a] = min(M.dims[a] - 1, (int) floorf((q[a] + r - M.origin[a]) * M.inv_cell));
-  }
-  for (int cz = lo[2]; cz <= hi[2]; ++cz)
-    for (int cy = lo[1]; cy <= hi[1]; ++cy) {
-      const uint32_t row = ((uint32_t) cz * (uint32_t) M.dims[1] + (uint32_t) cy) * (uint32_t) M.dims[0];
-      if (lo[0] > hi[0]) continue;
-      const uint32_t b = M.cell_start[row + lo[0]], e = M.cell_start[row + hi[0] + 1];  // cells of one row are contiguous
-      for (uint32_t i = b; i < e; ++i) {
-        const float4 a4 = M.pa[i];
-        const V3 dif = v3(a4.x, a4.y, a4.z) - pos;
-        const float dist2 = length2(dif);
-        if (dist2 < h.dist2[0]) {
-          const float4 b4 = M.pb[i];
-          if (dot(v3(b4.x, b4.y, b4.z), N) >= 0) continue;  // the photon arrived from behind the surface
-          heap_offer(h, dist2, i);
-        }
-      }
+  uint32_t stack[64];  // (index << 2) | stage; the tree is balanced: depth <= 32
+  int sp = 0;
+  stack[sp++] = 1u << 2;
+  while (sp) {
+    const uint32_t e = stack[--sp];
+    const uint32_t idx = e >> 2, stage = e & 3u;
+    if (stage == 2u || (int) idx >= M.half) {
+      photon_visit(M, idx, pos, N, h);
+      continue;
     }
+    const float4 a4 = M.pa[idx];
+    const int axis = (int) ((__float_as_uint(M.pb[idx].w) >> 24) & 3u);
+    const float p_axis = axis == 0 ? a4.x : (axis == 1 ? a4.y : a4.z);
+    const float dist = q[axis] - p_axis;
+    if (stage == 0u) {
+      stack[sp++] = (idx << 2) | 1u;
+      stack[sp++] = (dist > 0 ? 2u * idx + 1u : 2u * idx) << 2;
+    } else {
+      stack[sp++] = (idx << 2) | 2u;
+      if (dist * dist < h.dist2[0]) stack[sp++] = (dist > 0 ? 2u * idx : 2u * idx + 1u) << 2;
+    }
+  }
   for (int i = 1; i <= h.found; i++) {
     const float4 a4 = M.pa[h.id[i]], b4 = M.pb[h.id[i]];
-    const uint32_t c = __float_as_uint(b4.w);
+    const uint32_t c = __float_as_uint(b4.w);  // low 24 bits: the Color24
     const V3 power = v3((float) (c & 255u) / 255.0f, (float) ((c >> 8) & 255u) / 255.0f, (float) ((c >> 16) & 255u) / 255.0f) * a4.w;
     const float filter = 1 - h.dist2[i] / h.dist2[0];
     irrad = irrad + filter * power;

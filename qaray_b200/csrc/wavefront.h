@@ -50,18 +50,16 @@ namespace qb {
 #define QB_AREA_SPP_MIN 16     // GenLight::shadow_spp_min (lights.cpp:16)
 #define QB_AREA_SPP_MAX 64     // GenLight::shadow_spp_max (lights.cpp:17)
 
-// Photon map as the gather kernel reads it (photon.cuh): photons sorted by the cell of a uniform grid over their bounds
-// (cell edge >= the gather radius, so a query looks at 3 x 3 x 3 cells), dequantised the way cyPhotonMap::Photon::GetPower /
-// GetDirection return them (src/ext/cyPhotonMap.h:61-70,186-206).
+// Photon map as the gather kernel reads it (photon.cuh): cyPhotonMap's own left-balanced kd-tree (src/ext/cyPhotonMap.h:226-318),
+// photon i of the tree at index i (index 0 unused, children of i at 2 i and 2 i + 1), dequantised the way
+// Photon::GetPower / GetDirection return them (:61-70,186-206). The tree — not just any nearest-neighbour structure — is kept
+// because LocatePhotons' result depends on the ORDER candidates arrive in (see photon.cuh).
 struct DPhotonMap {
-  const float4 *pa;            // position.xyz, max power (Photon::power after ScalePhotonPowers)
-  const float4 *pb;            // direction.xyz, colour bits (r | g << 8 | b << 16 of the Color24)
-  const uint32_t *cell_start;  // dims.x * dims.y * dims.z + 1 offsets
-  float origin[3];
-  float inv_cell;
-  int32_t dims[3];
-  uint32_t count;
-  float radius;                // PhotonMap::radius of the scene (renderer.cpp:123-127)
+  const float4 *pa;   // position.xyz, max power (Photon::power after ScalePhotonPowers)
+  const float4 *pb;   // direction.xyz, bits: colour r | g << 8 | b << 16, splitting plane << 24
+  uint32_t count;     // photons (tree indices 1 .. count)
+  int32_t half;       // halfStoredPhotons: nodes with index < half are descended (cyPhotonMap.h:247)
+  float radius;       // PhotonMap::radius of the scene (renderer.cpp:123-127)
 };
 
 struct WfBuffers {

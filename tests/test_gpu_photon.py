@@ -66,12 +66,17 @@ def test_emission_matches_reference(name, which):
     # libm differences (sinf / cosf / powf in the last ulp) may flip a lobe choice or a grazing hit now and then
     assert same.mean() >= 0.995, "%d of %d emissions store a different number of photons" % ((~same).sum(), n)
     off = np.concatenate([[0], np.cumsum(ref_counts)])
-    bad = 0
+    bad = bad_first = 0
+    close = lambda a, b: bool((np.abs(a[..., :6] - b[..., :6]) <= 2e-4 + 2e-4 * np.abs(b[..., :6])).all() and
+                              (np.abs(a[..., 6:] - b[..., 6:]) <= 1e-6 + 5e-4 * np.abs(b[..., 6:])).all())
     for e in np.nonzero(same & (ref_counts > 0))[0]:
         a, b = rec[e, :counts[e]], ref_ph[off[e]:off[e + 1]]
-        ok = (np.abs(a[:, :6] - b[:, :6]) <= 2e-4 + 2e-4 * np.abs(b[:, :6])).all() and (np.abs(a[:, 6:] - b[:, 6:]) <= 1e-6 + 5e-4 * np.abs(b[:, 6:])).all()
-        bad += not ok
-    assert bad <= max(2, int(0.005 * n)), "%d emissions differ in position / direction / power" % bad
+        bad += not close(a, b)
+        bad_first += not close(a[0], b[0])
+    # a path of up to 20 bounces amplifies last-ulp differences of sinf / cosf / powf: the first stored photon of an emission
+    # (one or two bounces in) must agree, whole paths may drift apart in a few per cent of the emissions
+    assert bad_first <= max(2, int(0.005 * n)), "%d emissions differ in their first photon" % bad_first
+    assert bad <= int(0.03 * n), "%d emissions differ in position / direction / power" % bad
 
 
 @pytest.mark.parametrize("name,which", cases())
@@ -127,11 +132,11 @@ def test_build_fills_the_maps_by_the_reference_rule():
         want = flat[:size, 6:].max(axis=1) * (np.float32(1.0) / np.float32(emitted))
         assert np.allclose(pw.max(axis=1), want, rtol=4.1e-3)  # 255 * c / power may truncate to 254 for the largest channel itself
     # deterministic: the same seed gives the same maps whatever the batch
-    pos2 = np.zeros((5000, 3), np.float32)
+    pos1, pos2 = np.zeros((5000, 3), np.float32), np.zeros((5000, 3), np.float32)
+    capi.check(lib, lib.qg_photon_map_read(h, 0, _p(pos1), None, None, 5000, None))
     capi.check(lib, lib.qg_photon_maps_build(h, C.byref(pp), None))
     capi.check(lib, lib.qg_photon_map_read(h, 0, _p(pos2), None, None, 5000, None))
-    capi.check(lib, lib.qg_photon_map_read(h, 0, _p(pos), None, None, 5000, None))
-    assert np.array_equal(pos, pos2)
+    assert np.array_equal(pos1, pos2) and pos1.any()
     lib.qg_photon_maps_clear(h)
     rp = capi.RenderParams(1, 5, 1, 0x5EED, 32, 24, 0, 1, 0, 0, 0, 0, 0, 0, 1)
     assert lib.qg_render(h, C.byref(rp), None, None, None, None, None, None) == capi.QG_EINVAL  # maps cleared: refuse loudly
