@@ -232,7 +232,7 @@ def run_b200_arm(args):
     if world > 1:
         # NCCL_DEBUG stays as the operator set it (the rank count / transport lines are evidence); NCCL writes its log to
         # stdout by default, which carries the one JSON line, so the log goes to stderr unless a file was asked for
-        if os.environ.get("NCCL_DEBUG") and not os.environ.get("NCCL_DEBUG_FILE"):
+        if not os.environ.get("NCCL_DEBUG_FILE"):  # also without NCCL_DEBUG: the version banner goes where the log goes
             os.environ["NCCL_DEBUG_FILE"] = "/dev/stderr"
         dist.init_process_group("nccl", device_id=dev)
     lib = capi.load()
@@ -368,9 +368,15 @@ def run_b200_arm(args):
             capi.check(lib, lib.qg_render_accumulate(h, C.byref(whole), C.c_void_p(accum.data_ptr()), C.c_void_p(depth.data_ptr()), sptr, None))
             torch.cuda.synchronize()
             a, b = red.view(-1, 4)[:, :3].double() / spp_total, accum.view(-1, 4)[:, :3].double() / spp_total
+            # the reference's own arithmetic yields a few non-finite samples on the textured scenes (0/0 in its texture filter),
+            # reproduced here: they must be the same pixels on both sides; the rest is compared
+            fa, fb = torch.isfinite(a).all(dim=1), torch.isfinite(b).all(dim=1)
+            m = fa & fb
+            a, b = a[m], b[m]
             image_check = {"what": "NCCL-reduced %d-GPU frame vs the same %d-spp frame rendered on one GPU (linear radiance means)" % (world, spp_total),
                            "max_abs": float((a - b).abs().max()), "rmse": float(((a - b) ** 2).mean().sqrt()),
                            "max_rel": float(((a - b).abs() / (b.abs() + 1e-3)).max()), "mean": float(b.mean()),
+                           "nonfinite_pixels": [int((~fa).sum()), int((~fb).sum())], "nonfinite_same_pixels": bool(torch.equal(fa, fb)),
                            "weights_equal": bool(torch.equal(red.view(-1, 4)[:, 3], accum.view(-1, 4)[:, 3]))}
         dist.barrier()
     return finish_b200(args, locals())
@@ -431,8 +437,8 @@ def finish_b200(args, L):
             peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
         else:
             peak, peak_src = 6650.0, "B200_PROFILING.md fallback (of fallback)"
-        # launches per wave = 1 (stats) + (bounce + 1) x (trace + 2 cull-check kernels + finish + shade [+ shadow]); waves per step follow
-        per_wave = 1 + (BOUNCE + 1) * (5 + (1 if t["shadow"] > 0 else 0))
+        # launches per wave = 1 (stats) + (bounce + 1) x (trace + 2 cull-check kernels + finish + shade [+ shadow + its exact walk]); waves per step follow
+        per_wave = 1 + (BOUNCE + 1) * (5 + (2 if t["shadow"] > 0 else 0))
         n_waves = max(1, int(round(t["launches"] / float(args.steps) / per_wave)))
         achieved = kbytes / (kms * 1e-3) * 1e-9 if kms > 0 else 0.0
         traffic = None

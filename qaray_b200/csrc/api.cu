@@ -476,6 +476,9 @@ int ensure_wf(qgScene *sc, uint32_t capacity, bool carry_diff = false)
     CU(cudaMemset(B.amask, 0, area_cap * 2 * sizeof(uint32_t)));
     B.area_capacity = (uint32_t) area_cap;
   }
+  B.anyq_capacity = 1u << 22;  // beyond this the lanes repeat the mesh themselves (exact, slower)
+  CU(cudaMalloc((void **) &B.anyq, (size_t) B.anyq_capacity * sizeof(uint32_t)));
+  sc->wf_allocs.push_back(B.anyq);
   B.redo_capacity = 1u << 18;
   CU(cudaMalloc((void **) &B.redo, (size_t) B.redo_capacity * sizeof(uint4)));
   sc->wf_allocs.push_back(B.redo);
@@ -700,12 +703,12 @@ void run_wave(qgScene *sc, WfParams P, cudaStream_t st, uint64_t *launches, Kern
       if (sc->dev.num_nonambient > 0) {
         launch_wf_shadow(sc->dev, B, P, gsh, st2);
         if (clk) clk->stamp(2, st2);
-        *launches += 1;
+        *launches += 2;  // any-hit traversal + the warp-per-ray exact walk of what it handed over
       }
       if (sc->dev_num_area > 0) {
         launch_wf_area(sc->dev, B, P, gsh, st2);
         if (clk) clk->stamp(2, st2);
-        *launches += 2;
+        *launches += 3;
       }
       if (st2 != st) {
         cudaEventRecord(sc->ev_shadow, st2);

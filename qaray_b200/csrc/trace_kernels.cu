@@ -10,6 +10,7 @@
 // long rays do not hold back a statically assigned tail and no host sync is needed between bounces.
 #include "traverse.cuh"
 #include "blockpool.cuh"
+#include "anyexact.cuh"
 #include "wavefront.h"
 #include <algorithm>
 #include <map>
@@ -164,7 +165,12 @@ struct WfShadowIO {
   __device__ uint32_t *cursor() { return &B.counters[QB_CNT_FETCH_SHADOW + P.depth]; }
   __device__ uint32_t map(uint32_t q) const { return q; }                 // queue position -> ray index
   __device__ bool exact(uint32_t, int) const { return false; }  // true: walk this mesh with the degenerate-axis cull off
-  __device__ bool defer(uint32_t, int, float) const { return false; }      // false: the lane repeats the mesh itself
+  __device__ AnyQueue any_queue() const
+  {
+    return AnyQueue{B.anyq, B.anyq_capacity, &B.counters[QB_CNT_ANYQ + P.depth], &B.counters[QB_CNT_FETCH_ANYQ + P.depth]};
+  }
+  // true: the whole ray goes to k_any_exact (a warp walks it as the reference does); false: the lane repeats the mesh itself
+  __device__ bool defer(uint32_t idx, int, float) const { return any_push(any_queue(), idx); }
   __device__ bool load(uint32_t idx, Ray3 &c, float &tmax)
   {
     const float4 a = B.s0[idx], b = B.s1[idx];
@@ -339,6 +345,17 @@ __global__ void QB_TRACE_BOUNDS_ANY k_wf_shadow(const DScene S, const WfBuffers 
   flush_counters(B.stats, cnt, 5);
 }
 
+// the any-hit rays k_wf_shadow handed over (anyexact.cuh): a warp per ray, the reference's own walk
+__global__ void __launch_bounds__(QB_ANYX_WARPS * 32) k_any_exact_shadow(const DScene S, const WfBuffers B, const WfParams P)
+{
+  __shared__ uint32_t s_stack[QB_ANYX_WARPS * QB_ANYX_STACK];
+  if (B.counters[QB_CNT_ANYQ + P.depth] == 0u) return;
+  TraceCounters cnt = {0, 0, 0};
+  WfShadowIO io{B, P, 0u};
+  any_exact_pass(S, io, io.any_queue(), s_stack, cnt);
+  flush_counters(B.stats, cnt, 5);
+}
+
 // ---- area lights: PointLight / SpotLight with size > 0.01 (src/lights/lights.cpp:50-65,84-101) -----------------------------
 // The reference estimates such a light's visibility with 16 shadow rays toward `position + UniformBall(size)`, and 64 when
 // the running estimate ever lies strictly between 0 and 1. Sample s of a group is a pure function of (group key, s), so
@@ -353,7 +370,11 @@ struct WfAreaIO {
   __device__ uint32_t *cursor() { return &B.counters[QB_CNT_FETCH_AREA + P.depth]; }
   __device__ uint32_t map(uint32_t q) const { return q; }                 // queue position -> ray index
   __device__ bool exact(uint32_t, int) const { return false; }  // true: walk this mesh with the degenerate-axis cull off
-  __device__ bool defer(uint32_t, int, float) const { return false; }      // false: the lane repeats the mesh itself
+  __device__ AnyQueue any_queue() const
+  {
+    return AnyQueue{B.anyq, B.anyq_capacity, &B.counters[QB_CNT_ANYQ_AREA + P.depth], &B.counters[QB_CNT_FETCH_ANYQ_AREA + P.depth]};
+  }
+  __device__ bool defer(uint32_t idx, int, float) const { return any_push(any_queue(), idx); }
   __device__ bool load(uint32_t idx, Ray3 &c, float &tmax)
   {
     const uint32_t g = idx / QB_AREA_SPP_MAX;
@@ -380,6 +401,16 @@ __global__ void QB_TRACE_BOUNDS_ANY k_wf_area_shadow(const DScene S, const WfBuf
   TraceCounters cnt = {0, 0, 0};
   WfAreaIO io{S, B, P, min(B.counters[QB_CNT_AREA + P.depth], B.area_capacity) * (uint32_t) QB_AREA_SPP_MAX};
   QB_TRAVERSE(true, io, cnt);
+  flush_counters(B.stats, cnt, 5);
+}
+
+__global__ void __launch_bounds__(QB_ANYX_WARPS * 32) k_any_exact_area(const DScene S, const WfBuffers B, const WfParams P)
+{
+  __shared__ uint32_t s_stack[QB_ANYX_WARPS * QB_ANYX_STACK];
+  if (B.counters[QB_CNT_ANYQ_AREA + P.depth] == 0u) return;
+  TraceCounters cnt = {0, 0, 0};
+  WfAreaIO io{S, B, P, 0u};
+  any_exact_pass(S, io, io.any_queue(), s_stack, cnt);
   flush_counters(B.stats, cnt, 5);
 }
 
@@ -459,11 +490,13 @@ struct RayBufAnyIO {
   uint32_t n;
   uint32_t *cur;
   uint8_t *occ;
+  AnyQueue Q;
+  __device__ AnyQueue any_queue() const { return Q; }
   __device__ uint32_t count() const { return n; }
   __device__ uint32_t *cursor() { return cur; }
   __device__ uint32_t map(uint32_t q) const { return q; }                 // queue position -> ray index
   __device__ bool exact(uint32_t, int) const { return false; }  // true: walk this mesh with the degenerate-axis cull off
-  __device__ bool defer(uint32_t, int, float) const { return false; }      // false: the lane repeats the mesh itself
+  __device__ bool defer(uint32_t idx, int, float) const { return any_push(Q, idx); }
   __device__ bool load(uint32_t idx, Ray3 &c, float &tmax)
   {
     c.p = v3(rays6[6 * idx + 0], rays6[6 * idx + 1], rays6[6 * idx + 2]);
@@ -519,6 +552,15 @@ __global__ void QB_TRACE_BOUNDS_ANY k_trace_any_rays(const DScene S, RayBufAnyIO
 {
   TraceCounters cnt = {0, 0, 0};
   QB_TRAVERSE(true, io, cnt);
+  flush_counters(stats, cnt, 5);
+}
+
+__global__ void __launch_bounds__(QB_ANYX_WARPS * 32) k_any_exact_rays(const DScene S, RayBufAnyIO io, unsigned long long *stats)
+{
+  __shared__ uint32_t s_stack[QB_ANYX_WARPS * QB_ANYX_STACK];
+  if (*io.Q.count == 0u) return;
+  TraceCounters cnt = {0, 0, 0};
+  any_exact_pass(S, io, io.Q, s_stack, cnt);
   flush_counters(stats, cnt, 5);
 }
 
@@ -635,10 +677,12 @@ void launch_wf_trace(const DScene &S, const WfBuffers &B, const WfParams &P, int
 void launch_wf_shadow(const DScene &S, const WfBuffers &B, const WfParams &P, int grid, cudaStream_t st)
 {
   QB_LAUNCH_TRACE(k_wf_shadow, grid, st, S, B, P);
+  k_any_exact_shadow<<<qb_sms() * 4, QB_ANYX_WARPS * 32, 0, st>>>(S, B, P);
 }
 void launch_wf_area(const DScene &S, const WfBuffers &B, const WfParams &P, int grid, cudaStream_t st)
 {
   QB_LAUNCH_TRACE(k_wf_area_shadow, grid, st, S, B, P);
+  k_any_exact_area<<<qb_sms() * 4, QB_ANYX_WARPS * 32, 0, st>>>(S, B, P);
   k_wf_area_resolve<<<qb_sms() * 8, QB_BLOCK, 0, st>>>(S, B, P);
 }
 static int flat_grid(size_t n)
@@ -687,8 +731,13 @@ void launch_trace_any_rays(const DScene &S, const float *rays6, const float *tma
 {
   uint32_t *cur = (uint32_t *) scratch;
   cudaMemsetAsync(cur, 0, 16, st);
-  RayBufAnyIO io{rays6, tmax, (uint32_t) n, cur, occ};
+  // scratch: 16-byte header (work cursor, hand-over count, hand-over cursor), then the hand-over queue (one index per ray)
+  // QB_ANYQ_CAP: test hook — a smaller queue, so the in-lane repeat of a full queue is exercised as well
+  uint32_t qcap = (uint32_t) n;
+  if (const char *e = getenv("QB_ANYQ_CAP")) qcap = (uint32_t) std::min<size_t>(n, (size_t) std::max(0, atoi(e)));
+  RayBufAnyIO io{rays6, tmax, (uint32_t) n, cur, occ, AnyQueue{(uint32_t *) ((char *) scratch + 16), qcap, cur + 1, cur + 2}};
   QB_LAUNCH_TRACE(k_trace_any_rays, trace_grid_for(n), st, S, io, stats);
+  k_any_exact_rays<<<qb_sms() * 4, QB_ANYX_WARPS * 32, 0, st>>>(S, io, stats);
 }
 void launch_primary_rays(const WfParams &P, size_t n, qgRay *out, cudaStream_t st)
 {

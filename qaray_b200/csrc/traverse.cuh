@@ -426,22 +426,31 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
       for (int rep = 0; rep < QB_NEXT_REPS; ++rep) {
       const bool go_next = active && cur == QB_REF_EMPTY;
       if (rep > 0 && 2 * __popc(__ballot_sync(0xFFFFFFFFu, go_next)) < n_next) break;
-      bool redo = false;
+      bool redo = false, handed_over = false;
       if (go_next && k > 0 && cull_state == 1) {
         // the cull dropped boxes and the mesh produced no hit inside its own box: repeat it exactly as the reference walks it
         cull_state = 0;
         // closest-hit rays of the wavefront hand the check to k_redo_detect / k_redo_exact (trace_kernels.cu) and go on: a
         // single lane repeating a whole mesh costs up to ~30 ms, and some sample ranges hold a few dozen such rays
         const float z_entry = CWF(CW_ZENTRY);
-        if (!(hz <= CWF(CW_ZSANE)) && (ANY || !io.defer(idx, k - 1, z_entry))) {
-          redo = true;
-          cull_state = 2;
-          hz = z_entry;
-          obj_slot = -1; CW(CW_UVSLOT) = 0xFFFFFFFFu; sp = 0;
-          cur = __float_as_uint(obj_rec(S, T, k - 1).lo.w);
+        if (!(hz <= CWF(CW_ZSANE))) {
+          // any-hit rays (a directional light's shadow ray has no far end: every unoccluded one lands here when its direction
+          // has a degenerate axis in the mesh's frame) hand the WHOLE ray to k_any_exact, which walks it as the reference
+          // does with a warp per ray; the lane drops it. A full queue, and the closest-hit rays of the ray-buffer / redo
+          // passes whose queue is full, repeat the mesh here.
+          if (ANY && io.defer(idx, k - 1, z_entry)) {
+            active = false;
+            handed_over = true;
+          } else if (ANY || !io.defer(idx, k - 1, z_entry)) {
+            redo = true;
+            cull_state = 2;
+            hz = z_entry;
+            obj_slot = -1; CW(CW_UVSLOT) = 0xFFFFFFFFu; sp = 0;
+            cur = __float_as_uint(obj_rec(S, T, k - 1).lo.w);
+          }
         }
       }
-      if (go_next && !redo) {
+      if (go_next && !redo && !handed_over) {
         if (!ANY && k > 0 && obj_slot >= 0) {
           CW(CW_HK) = (uint32_t) (k - 1); CW(CW_HSLOT) = (uint32_t) obj_slot; CW(CW_HLASTTRI) = (uint32_t) obj_slot;
           const uint32_t uv_slot = CW(CW_UVSLOT);

@@ -37,7 +37,11 @@ namespace qb {
 #define QB_CNT_HOLES_PATHS 144  // [144 .. 159] dead entries in the path queue of depth d (unused tails of the shade warps' reservations)
 #define QB_CNT_HOLES_SHADOW 160 // [160 .. 175] dead entries in the shadow queue of depth d
 #define QB_CNT_GATHER 176      // [176 .. 191] photon-map gather requests queued by shade(d) (-use-photon-map)
-#define QB_CNT_WORDS 192
+#define QB_CNT_ANYQ 192            // [192 .. 207] shadow rays of depth d handed to k_any_exact (anyexact.cuh)
+#define QB_CNT_FETCH_ANYQ 208      // [208 .. 223] its work cursor
+#define QB_CNT_ANYQ_AREA 224       // [224 .. 239] the same for the area-light shadow samples
+#define QB_CNT_FETCH_ANYQ_AREA 240 // [240 .. 255]
+#define QB_CNT_WORDS 256
 
 // area lights (PointLight / SpotLight with size > 0.01, src/lights/lights.cpp:50-65,84-101): shadow samples per group
 #ifndef QB_SHADE_CHUNK
@@ -98,6 +102,9 @@ struct WfBuffers {
   float4 *g2;  // V.z, diffuse.rgb
   float4 *g3;  // specular.rgb, glossiness
   float4 *g4;  // throughput.rgb, accum slot | maps << 30 (bit 30 photon map, bit 31 caustics map)
+  // any-hit rays handed to the warp-per-ray exact walk (anyexact.cuh): ray indices
+  uint32_t *anyq;
+  uint32_t anyq_capacity;
   // material sort of the shade queue (optional): permutation and the per-material bins / offsets
   uint32_t *perm;      // capacity entries
   uint32_t *mat_bins;  // 2 * QB_MAT_BINS: counts, then running offsets
