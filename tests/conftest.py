@@ -21,7 +21,7 @@ def pytest_configure(config):
 def golden_names():
     if not os.path.isdir(GOLDEN_DIR):
         return []
-    return sorted(f[:-4] for f in os.listdir(GOLDEN_DIR) if f.endswith(".npz") and not f.startswith(("img_", "imghi_", "cls_", "feat_", "edge_", "rays_", "photon_")))
+    return sorted(f[:-4] for f in os.listdir(GOLDEN_DIR) if f.endswith(".npz") and not f.startswith(("img_", "imghi_", "cls_", "feat_", "edge_", "rays_", "photon_", "cliff_")))
 
 
 CLASS_ID = {"pathtracing": 1, "montecarlogi": 2, "blinn_basic": 3, "phong_basic": 4}  # QG_CLASS_* (include/qaray_b200.h)
