@@ -203,6 +203,13 @@ const char *qg_host_scene_log(const qgHostScene *hs); /* what the reference woul
 void qg_host_scene_destroy(qgHostScene *hs);
 /* Same, from an already flattened scene (what a C++ binding fills from qaray::Scene, src/scene/scene.h:55-67). */
 int qg_scene_create(const qgSceneDesc *desc, qgScene **out);
+/* The BVH built for `mesh`, in the array form of the reference's cyBVH (src/ext/cyBVH.h:63-166: BVH::Build with MeanSplit,
+ * ConvertTempData; TriObj::Load builds it with 4 elements per leaf, src/objects/objects.h:71): slot 0 unused, root = 1, sibling
+ * nodes adjacent. boxes6 = min xyz, max xyz per slot; data = the node word (leaf: bit 31 | (count - 1) << 28 | element
+ * offset; internal: index of the first child); elements = face ids in leaf order. Host only (no device needed) — lets a
+ * binding or a test compare the topology with cyBVH's node for node. Any output may be NULL (sizes only). */
+int qg_mesh_bvh(const qgMesh *mesh, float *boxes6, uint32_t *data, int64_t node_capacity, int64_t *num_nodes, uint32_t *elements,
+                int64_t element_capacity, int64_t *num_elements);
 void qg_scene_destroy(qgScene *scene);
 int qg_scene_info(const qgScene *scene, qgSceneInfo *out);
 /* copies the flattened node table (num_nodes entries) — lets a binding check its transforms */

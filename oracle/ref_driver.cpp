@@ -38,6 +38,10 @@
 #define private public
 #include "samplers/Sampler_Marsaglia.h"
 #undef private
+// TriObj keeps its cyBVH private; qaref_bvh_dump reads it through cyBVH's public node accessors
+#define private public
+#include "objects/objects.h"
+#undef private
 
 #include "scene/scene.h"
 #include "renderers/renderer.h"
@@ -178,6 +182,49 @@ void qaref_dump_nodes(int32_t *meta, float *xf)
     xf[21 * i + 19] = pos.y;
     xf[21 * i + 20] = pos.z;
   }
+}
+
+// The reference's own BVH of node `node_index`'s TriObj (cyBVH, built by TriObj::Load with 4 elements per leaf), read through
+// BVH's public accessors (src/ext/cyBVH.h:75-128) into cyBVH's array form: slot 0 unused, root 1; data = leaf: bit 31 |
+// (count - 1) << 28 | element offset, internal: first child. Returns the number of node slots (largest id + 1), 0 when the
+// node holds no mesh; *num_elems = NF.
+int64_t qaref_bvh_dump(int node_index, int64_t cap_nodes, float *boxes6, uint32_t *data, int64_t cap_elems, uint32_t *elements, int64_t *num_elems)
+{
+  if (node_index < 0 || node_index >= (int) g_nodes.size()) return 0;
+  Object *o = g_nodes[node_index]->GetNodeObj();
+  if (o == nullptr || o == &theSphere || o == &thePlane) return 0;
+  TriObj *t = static_cast<TriObj *>(o);
+  if (num_elems) *num_elems = (int64_t) t->NF();
+  if (t->NF() == 0) return 0;
+  const auto &bvh = t->bvh;
+  // element offsets are relative to the first element: the leftmost leaf holds offset 0
+  unsigned first = bvh.GetRootNodeID();
+  while (!bvh.IsLeafNode(first)) first = bvh.GetFirstChildNode(first);
+  const unsigned int *base = bvh.GetNodeElements(first);
+  std::vector<unsigned> stack(1, bvh.GetRootNodeID());
+  int64_t slots = 0;
+  while (!stack.empty()) {
+    const unsigned id = stack.back();
+    stack.pop_back();
+    slots = std::max<int64_t>(slots, (int64_t) id + 1);
+    if ((int64_t) id < cap_nodes) {
+      if (boxes6) memcpy(boxes6 + 6 * id, bvh.GetNodeBounds(id), 6 * sizeof(float));
+      if (bvh.IsLeafNode(id)) {
+        const unsigned cnt = bvh.GetNodeElementCount(id);
+        const unsigned off = (unsigned) (bvh.GetNodeElements(id) - base);
+        if (data) data[id] = 0x80000000u | ((cnt - 1) << 28) | off;
+        for (unsigned k = 0; k < cnt; ++k)
+          if (elements && (int64_t) off + k < cap_elems) elements[off + k] = bvh.GetNodeElements(id)[k];
+      } else if (data) {
+        data[id] = bvh.GetFirstChildNode(id);
+      }
+    }
+    if (!bvh.IsLeafNode(id)) {
+      stack.push_back(bvh.GetFirstChildNode(id));
+      stack.push_back(bvh.GetSecondChildNode(id));
+    }
+  }
+  return slots;
 }
 
 // out[14] = pos3, dir3, up3, fovy, focal, dof, W, H

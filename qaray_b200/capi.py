@@ -125,6 +125,7 @@ PROTOTYPES = {
     "qg_scene_info": (C.c_int, [vp, C.POINTER(SceneInfo)]),
     "qg_scene_nodes": (C.c_int, [vp, C.POINTER(Node), i32]),
     "qg_trace_closest": (C.c_int, [vp, vp, C.c_size_t, vp]),
+    "qg_mesh_bvh": (C.c_int, [vp, vp, vp, C.c_int64, vp, vp, C.c_int64, vp]),
     "qg_trace_any": (C.c_int, [vp, vp, vp, C.c_size_t, vp]),
     "qg_primary_rays": (C.c_int, [vp, vp, C.c_size_t, i32, i32, vp]),
     "qg_sample_radiance": (C.c_int, [vp, C.POINTER(RenderParams), vp, C.c_size_t, vp, vp]),

@@ -157,6 +157,20 @@ void put_texcolor_dev(const qgTexturedColor &q, DTexColor *o)
   o->identity = id ? 1 : 0;
 }
 
+// what the BVH build reads of a qgMesh: vertex positions and the faces' vertex indices
+bool mesh_positions(const qgMesh &m, ObjMesh *om)
+{
+  om->vertices.assign(m.vertices, m.vertices + 3 * (size_t) m.num_vertices);
+  om->faces.resize(m.num_faces);
+  for (int f = 0; f < m.num_faces; ++f)
+    for (int k = 0; k < 3; ++k) {
+      const int vi = m.face_indices[9 * f + 3 * k];
+      if (vi < 0 || vi >= m.num_vertices) return false;
+      om->faces[f].idx[k].v = vi;
+    }
+  return true;
+}
+
 int upload_scene(qgScene *sc)
 {
   const FlatScene &F = sc->flat;
@@ -202,14 +216,7 @@ int upload_scene(qgScene *sc)
   for (size_t mi = 0; mi < F.meshes.size(); ++mi) {
     const qgMesh &m = F.meshes[mi];
     ObjMesh om;
-    om.vertices.assign(m.vertices, m.vertices + 3 * (size_t) m.num_vertices);
-    om.faces.resize(m.num_faces);
-    for (int f = 0; f < m.num_faces; ++f)
-      for (int k = 0; k < 3; ++k) {
-        const int vi = m.face_indices[9 * f + 3 * k];
-        if (vi < 0 || vi >= m.num_vertices) return fail(QG_EINVAL, "mesh face references a missing vertex");
-        om.faces[f].idx[k].v = vi;
-      }
+    if (!mesh_positions(m, &om)) return fail(QG_EINVAL, "mesh face references a missing vertex");
     CyBvh cy;
     build_cy_bvh(om, 4, &cy);  // TriObj::Load: bvh.SetMesh(this, 4) (objects.h:71)
     DMesh &dm = meshes[mi];

@@ -108,18 +108,22 @@ class Renderer_B200 {
     sampleCountBuffer.assign(n, 0);
     maskBuffer.assign(n, 0);
     linearBuffer.assign(3 * n, 0.f);
-    // Initialize Photon Map (renderer.cpp:115-291); "TODO: Photon Map for MPI Mode" there: single-GPU here as well
+    // Initialize Photon Map (renderer.cpp:115-291). The reference leaves "TODO: Photon Map for MPI Mode"; here every GPU of
+    // -gpus N builds the maps on its own scene replica from the same seed — emission e draws from the stream of (e, map, seed),
+    // so the replicas hold identical maps and the shards gather from the same photons
     if (param.usePhotonMap && param.photonMapSize > 0 && param.causticsMapSize > 0) {
-      if (multi) { fprintf(stderr, "Renderer_B200: -use-photon-map and -gpus do not combine\n"); return false; }
       qgPhotonParams pp{};
       pp.photon_map_size = (int32_t) param.photonMapSize; pp.photon_map_bounce = (int32_t) param.photonMapBounce;
       pp.photon_map_radius = param.photonMapRadius;
       pp.caustics_map_size = (int32_t) param.causticsMapSize; pp.caustics_map_bounce = (int32_t) param.causticsMapBounce;
       pp.caustics_map_radius = param.causticsMapRadius;
       pp.seed = param.seed;
-      if (qg_photon_maps_build(scene, &pp, &photonStats) != QG_OK) {
-        fprintf(stderr, "Renderer_B200::ComputeScene: %s\n", qg_last_error());
-        return false;
+      for (int g = 0; g < (multi ? numGpus : 1); ++g) {
+        qgScene *replica = multi ? qg_multi_scene(multi, g) : scene;
+        if (qg_photon_maps_build(replica, &pp, g == 0 ? &photonStats : nullptr) != QG_OK) {
+          fprintf(stderr, "Renderer_B200::ComputeScene: %s\n", qg_last_error());
+          return false;
+        }
       }
       printf("\nPhoton Map: %llu photons, Caustics Map: %llu photons, %.3f ms\n", (unsigned long long) photonStats.photons[0],
              (unsigned long long) photonStats.photons[1], photonStats.device_ms);

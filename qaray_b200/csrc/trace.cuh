@@ -31,6 +31,38 @@ struct TraceCounters {
 
 __device__ __forceinline__ V3 xyz(float4 v) { return v3(v.x, v.y, v.z); }
 
+// One 64-byte geometry record (DBvhNode, DTri) into four float4. QB_LD256: two 256-bit loads (LDG.E.256, sm_100) instead of
+// four 128-bit ones — every lane reads a different record, so each load instruction costs one L1 tag look-up per lane and the
+// wide form halves them. QB_GEOM_EVICT_LAST: the records additionally stay in L2 ahead of the streaming wave state.
+#ifndef QB_LD256
+#define QB_LD256 0
+#endif
+#ifndef QB_GEOM_EVICT_LAST
+#define QB_GEOM_EVICT_LAST 0
+#endif
+__device__ __forceinline__ void ld_rec64(const void *p, float4 &a, float4 &b, float4 &c, float4 &d)
+{
+#if QB_LD256
+#if QB_GEOM_EVICT_LAST
+#define QB_LD256_OP "ld.global.nc.L2::evict_last.v8.f32"
+#else
+#define QB_LD256_OP "ld.global.nc.v8.f32"
+#endif
+  asm(QB_LD256_OP " {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+      : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
+      : "l"(p));
+  asm(QB_LD256_OP " {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+      : "=f"(c.x), "=f"(c.y), "=f"(c.z), "=f"(c.w), "=f"(d.x), "=f"(d.y), "=f"(d.z), "=f"(d.w)
+      : "l"((const char *) p + 32));
+#else
+  const float4 *q = (const float4 *) p;
+  a = __ldg(q);
+  b = __ldg(q + 1);
+  c = __ldg(q + 2);
+  d = __ldg(q + 3);
+#endif
+}
+
 // Node::ToNodeCoords(Ray): p' = itm*(p-pos); dir' = itm*((p+dir)-pos) - p'   (not itm*dir: the rounding differs)
 __device__ __forceinline__ Ray3 to_node(const DNode *__restrict__ n, Ray3 r)
 {

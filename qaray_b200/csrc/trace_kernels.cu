@@ -75,11 +75,32 @@ __device__ __forceinline__ void flush_counters(unsigned long long *stats, const 
 }
 
 // ---- IO policies of traverse_pool ------------------------------------------------------------------------------------
+// QB_STREAM_CS: the wave state is read and written once per launch — mark it evict-first (ld/st.global.cs) so that it does
+// not push the scene's records out of L2
+#ifndef QB_STREAM_CS
+#define QB_STREAM_CS 0
+#endif
+__device__ __forceinline__ float4 ld_stream(const float4 *p)
+{
+#if QB_STREAM_CS
+  return __ldcs(p);
+#else
+  return *p;
+#endif
+}
+__device__ __forceinline__ void st_stream(float4 *p, const float4 v)
+{
+#if QB_STREAM_CS
+  __stcs(p, v);
+#else
+  *p = v;
+#endif
+}
 // compact hit record of the wavefront: r0 = z, k, slot, tex_slot ; r1 = tex_t, tex_k, last_tri, -
 __device__ __forceinline__ void put_rec(float4 *r0, float4 *r1, uint32_t idx, const HitRec &h)
 {
-  r0[idx] = f4(h.z, __int_as_float(h.k), __int_as_float(h.slot), __int_as_float(h.tex_slot));
-  r1[idx] = f4(h.tex_t, __int_as_float(h.tex_k), __int_as_float(h.last_tri), 0.f);
+  st_stream(&r0[idx], f4(h.z, __int_as_float(h.k), __int_as_float(h.slot), __int_as_float(h.tex_slot)));
+  st_stream(&r1[idx], f4(h.tex_t, __int_as_float(h.tex_k), __int_as_float(h.last_tri), 0.f));
 }
 // the same without touching r1.w: the cull-check pass keeps its flag bits there while a ray may be walked more than once
 __device__ __forceinline__ void put_rec_keep_w(float4 *r0, float4 *r1, uint32_t idx, const HitRec &h)
@@ -137,7 +158,7 @@ struct WfClosestIO {
       Ray3 x, y;
       primary_ray(P, i, j, s, c, x, y);
     } else {
-      const float4 a = B.ps0[P.depth & 1][idx], b = B.ps1[P.depth & 1][idx];
+      const float4 a = ld_stream(&B.ps0[P.depth & 1][idx]), b = ld_stream(&B.ps1[P.depth & 1][idx]);
       if (__float_as_int(b.z) < 0) {  // dead entry (shade_kernels.cu, OutRes): report a miss, trace nothing
         HitRec m;
         m.z = QB_BIGFLOAT; m.k = -1; m.slot = -1; m.tex_k = -1; m.tex_slot = -1; m.tex_t = 0.f; m.last_tri = -1;
@@ -173,7 +194,7 @@ struct WfShadowIO {
   __device__ bool defer(uint32_t idx, int, float) const { return any_push(any_queue(), idx); }
   __device__ bool load(uint32_t idx, Ray3 &c, float &tmax)
   {
-    const float4 a = B.s0[idx], b = B.s1[idx];
+    const float4 a = ld_stream(&B.s0[idx]), b = ld_stream(&B.s1[idx]);
     c.p = v3(a.x, a.y, a.z);
     c.d = v3(a.w, b.x, b.y);
     tmax = b.z;
@@ -293,8 +314,11 @@ __global__ void QB_TRACE_BOUNDS k_redo_exact(const DScene S, const WfBuffers B, 
 }
 
 // hit attributes of the wave's rays from the compact records, one thread per ray (full warps): h0..h3 for shade
+#ifndef QB_FINISH_BLOCKS
+#define QB_FINISH_BLOCKS 1
+#endif
 template <bool PRIMARY>
-__global__ void __launch_bounds__(QB_BLOCK) k_wf_finish(const DScene S, const WfBuffers B, const WfParams P)
+__global__ void __launch_bounds__(QB_BLOCK, QB_FINISH_BLOCKS) k_wf_finish(const DScene S, const WfBuffers B, const WfParams P)
 {
   const uint32_t n = PRIMARY ? P.n_paths : min(B.counters[QB_CNT_PATHS + P.depth], B.capacity);
   for (uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += gridDim.x * blockDim.x) {

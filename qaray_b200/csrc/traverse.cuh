@@ -252,8 +252,9 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
         if (rep > 0 && 2 * __popc(__ballot_sync(0xFFFFFFFFu, go)) < n_inner) break;
         if (go) {
           const DBvhNode *np = &S.bvh[cur];
-          const float4 na = __ldg(&np->a), nb = __ldg(&np->b), nc = __ldg(&np->c);
-          const uint4 ndr = __ldg(&np->d);
+          float4 na, nb, nc, nd4;
+          ld_rec64(np, na, nb, nc, nd4);
+          const uint2 ndr = make_uint2(__float_as_uint(nd4.x), __float_as_uint(nd4.y));
           QB_CNT(nodes);
           const float p00x = -(r.p.x - na.x) * drcp.x, p00y = -(r.p.y - na.y) * drcp.y, p00z = -(r.p.z - na.z) * drcp.z;
           const float p01x = -(r.p.x - na.w) * drcp.x, p01y = -(r.p.y - nb.x) * drcp.y, p01z = -(r.p.z - nb.y) * drcp.z;
@@ -354,7 +355,8 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
         cur = sp > 0 ? stk[(--sp) * QB_BLOCK] : QB_REF_EMPTY;
         for (uint32_t i = 0; i < count; ++i) {
           const DTri *tp = &S.tris[base + i];
-          const float4 ta = __ldg(&tp->a), tb = __ldg(&tp->b), tc = __ldg(&tp->c), td = __ldg(&tp->d);
+          float4 ta, tb, tc, td;
+          ld_rec64(tp, ta, tb, tc, td);
           QB_CNT(tris);
           float t;
           if (tri_accept(r, hz, xyz(ta), xyz(tb), xyz(tc), v3(ta.w, tb.w, tc.w), td.x, __float_as_int(td.y), t)) {
@@ -392,7 +394,8 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
           rr.d.x = __shfl_sync(0xFFFFFFFFu, r.d.x, o); rr.d.y = __shfl_sync(0xFFFFFFFFu, r.d.y, o); rr.d.z = __shfl_sync(0xFFFFFFFFu, r.d.z, o);
           if (have) {
             const DTri *tp = &S.tris[tb + (code & 7u)];
-            const float4 ta = __ldg(&tp->a), tb4 = __ldg(&tp->b), tc = __ldg(&tp->c), td = __ldg(&tp->d);
+            float4 ta, tb4, tc, td;
+            ld_rec64(tp, ta, tb4, tc, td);
             QB_CNT(tris);
             float t;
             const bool ok = tri_candidate(rr, xyz(ta), xyz(tb4), xyz(tc), v3(ta.w, tb4.w, tc.w), td.x, __float_as_int(td.y), t);

@@ -75,6 +75,58 @@ def test_rank_shards_sum_to_the_whole_frame(name, nranks, tile_split):
     assert np.allclose(acc[..., :3], ref_acc[..., :3], rtol=2e-5, atol=1e-5 * spp)
 
 
+def build_maps(lib, h, sizes=(5000, 300)):
+    pp = capi.PhotonParams.defaults(0x5EED)
+    pp.photon_map_size, pp.caustics_map_size = sizes
+    capi.check(lib, lib.qg_photon_maps_build(h, C.byref(pp), None))
+
+
+def test_photon_mapped_shards_sum_to_the_whole_frame():
+    """-use-photon-map under the rank model (the reference's own "TODO: Photon Map for MPI Mode", renderer.cpp:116): the maps are
+    a function of the seed, so every rank builds the same ones; the gather of a path depends on its (pixel, sample) stream only,
+    so the shards of a tile x sample split still add up to the single-GPU frame."""
+    lib = capi.load()
+    capi.check(lib, lib.qg_init(0))
+    name, spp, nranks, tile_split = "trc_mtl_glass", 8, 4, 2
+    h, W, H = load(lib, name)
+    W, H = W // 4, H // 4
+    build_maps(lib, h)
+    whole = capi.RenderParams(spp, 5, 1, 0x5EED, W, H, 0, 1, 0, 0, 0, 0)
+    whole.use_photon_map = 1
+    ref_acc, ref_dep, ref_st = accumulate(lib, h, whole, W, H)
+    # the ranks' scenes are replicas that built their own maps: a second scene stands in for them
+    h2, _, _ = load(lib, name)
+    build_maps(lib, h2)
+    acc = np.zeros_like(ref_acc, dtype=np.float64)
+    rays = 0
+    for r in range(nranks):
+        mine = capi.RenderParams()
+        capi.check(lib, lib.qg_shard_params(C.byref(whole), r, nranks, tile_split, C.byref(mine)))
+        assert mine.use_photon_map == 1
+        a, d, st = accumulate(lib, h2, mine, W, H)
+        acc += a
+        rays += st.closest_rays + st.shadow_rays
+    lib.qg_scene_destroy(h)
+    lib.qg_scene_destroy(h2)
+    assert np.array_equal(acc[..., 3], ref_acc[..., 3])
+    assert rays == ref_st.closest_rays + ref_st.shadow_rays
+    assert ref_acc[..., :3].sum() > 0
+    assert np.allclose(acc[..., :3], ref_acc[..., :3], rtol=1e-4, atol=1e-5 * spp)
+
+
+def test_cli_gpus_n_with_photon_maps(tmp_path):
+    if device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    pre1, pre2 = str(tmp_path) + os.sep + "one_", str(tmp_path) + os.sep + "two_"
+    common = ["-batch", "-spp", "8", "-use-photon-map", "-assets", ASSETS]
+    out1 = run_cli(common + ["-out", pre1, scene_xml("trc_mtl_glass")], str(tmp_path))
+    out2 = run_cli(common + ["-gpus", "2", "-out", pre2, scene_xml("trc_mtl_glass")], str(tmp_path))
+    assert "Photon Map: 10000 photons" in out1 and "Photon Map: 10000 photons" in out2
+    a = np.asarray(Image.open(pre1 + "colorBuffer.png").convert("RGB")).astype(np.int32)
+    b = np.asarray(Image.open(pre2 + "colorBuffer_MPI.png").convert("RGB")).astype(np.int32)
+    assert np.abs(a - b).max() <= 1
+
+
 def multi_render(lib, name, ndev, tile_split, spp, prefix=None):
     m = C.c_void_p()
     capi.check(lib, lib.qg_multi_create(None, ndev, C.byref(m)))
