@@ -219,6 +219,17 @@ int qg_scene_nodes(const qgScene *scene, qgNode *out, int32_t capacity);
 int qg_trace_closest(qgScene *scene, const qgRay *rays, size_t n, qgHit *out);
 /* Scene::TraceNodeShadow(rootNode, ray, hInfo with z = tmax) (src/scene/scene.cpp:35-46). rays6 = p, dir. */
 int qg_trace_any(qgScene *scene, const float *rays6, const float *tmax, size_t n, uint8_t *occluded);
+/* qg_trace_any without an allocation. NO COUNTERPART IN THE REFERENCE: added for callers
+ * that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * d_rays6 (6n floats), d_tmax (n floats) and d_occluded (n bytes) are DEVICE pointers on the scene's device. The launch's
+ * scratch (work cursor + the hand-over queue of the exact walk) is a static device array of 4 MiB + 256 B that every GPU
+ * loading the library holds until exit, so n <= QG_NOALLOC_MAX_RAYS; a larger n is refused with QG_EINVAL. The call makes no
+ * cudaMalloc / cudaFree and does not synchronise: work is enqueued on `stream` (a cudaStream_t; NULL = the scene's own
+ * stream) and d_occluded is complete once that stream has passed this point. All calls on one device share the scratch:
+ * calls that overlap on the GPU (different streams or threads) race — serialise them on one stream. Results are those of
+ * qg_trace_any, bit for bit. */
+#define QG_NOALLOC_MAX_RAYS (1 << 20)
+int qg_trace_any_noalloc(qgScene *scene, const float *d_rays6, const float *d_tmax, size_t n, uint8_t *d_occluded, void *stream);
 /* Primary DiffRay of pixel (i,j), sample s as PixelRender builds it (renderer.cpp:312-326). pix = i,j,s triples. */
 int qg_primary_rays(qgScene *scene, const int32_t *pix, size_t n, int32_t width, int32_t height, qgRay *out);
 /* One PixelRender loop body per (i,j,s) triple: the sample's radiance before accumulation (renderer.cpp:312-339). */

@@ -127,6 +127,7 @@ PROTOTYPES = {
     "qg_trace_closest": (C.c_int, [vp, vp, C.c_size_t, vp]),
     "qg_mesh_bvh": (C.c_int, [vp, vp, vp, C.c_int64, vp, vp, C.c_int64, vp]),
     "qg_trace_any": (C.c_int, [vp, vp, vp, C.c_size_t, vp]),
+    "qg_trace_any_noalloc": (C.c_int, [vp, vp, vp, C.c_size_t, vp, vp]),  # device pointers, stream; static scratch
     "qg_primary_rays": (C.c_int, [vp, vp, C.c_size_t, i32, i32, vp]),
     "qg_sample_radiance": (C.c_int, [vp, C.POINTER(RenderParams), vp, C.c_size_t, vp, vp]),
     "qg_render": (C.c_int, [vp, C.POINTER(RenderParams), vp, vp, vp, vp, vp, C.POINTER(RenderStats)]),

@@ -768,4 +768,50 @@ void launch_primary_rays(const WfParams &P, size_t n, qgRay *out, cudaStream_t s
   k_primary_rays<<<flat_grid(n), QB_BLOCK, 0, st>>>(P, n, out);
 }
 
+// ---- any-hit batch without an allocation (qg_trace_any_noalloc) --------------------------------------------------------------
+// The scratch of launch_trace_any_rays (16-byte header + one queue entry per ray) lives in a file-scope device array instead of
+// a cudaMalloc'ed buffer: header in the first 256 bytes, the hand-over queue of the warp-per-ray exact walk after it. Every
+// GPU that loads the library holds the 4 MiB + 256 B until exit. All calls on a device share it: calls that overlap on the GPU
+// (two streams, two threads) race on the cursor and the queue.
+static __device__ __align__(256) unsigned char g_noalloc_scratch[256 + 4 * (size_t) QB_NOALLOC_MAX_RAYS];
+
+// The array's name is a host-side stand-in in host code, not a device address: ask the runtime for the address once per device,
+// with that device current (the caller has made it current: use_scene).
+static cudaError_t noalloc_scratch(unsigned char **out)
+{
+  static std::mutex mu;
+  static unsigned char *addr[QB_NOALLOC_MAX_DEVICES] = {};
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= QB_NOALLOC_MAX_DEVICES) return cudaErrorInvalidDevice;
+  std::lock_guard<std::mutex> lock(mu);
+  if (!addr[dev]) {
+    void *p = nullptr;
+    e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+    if (e != cudaSuccess) return e;
+    addr[dev] = (unsigned char *) p;
+  }
+  *out = addr[dev];
+  return cudaSuccess;
+}
+
+cudaError_t launch_trace_any_rays_noalloc(const DScene &S, const float *rays6, const float *tmax, size_t n, uint8_t *occ,
+                                          unsigned long long *stats, cudaStream_t st)
+{
+  if (n > (size_t) QB_NOALLOC_MAX_RAYS) return cudaErrorInvalidValue;
+  unsigned char *scratch = nullptr;
+  cudaError_t e = noalloc_scratch(&scratch);
+  if (e != cudaSuccess) return e;
+  uint32_t *cur = (uint32_t *) scratch;
+  // the array keeps the last call's contents: the work cursor, the hand-over count and its cursor must start at zero; the
+  // queue entries below the count are all written before they are read
+  e = cudaMemsetAsync(cur, 0, 16, st);
+  if (e != cudaSuccess) return e;
+  RayBufAnyIO io{rays6, tmax, (uint32_t) n, cur, occ, AnyQueue{(uint32_t *) (scratch + 256), (uint32_t) n, cur + 1, cur + 2}};
+  QB_LAUNCH_TRACE(k_trace_any_rays, trace_grid_for(n), st, S, io, stats);
+  k_any_exact_rays<<<qb_sms() * 4, QB_ANYX_WARPS * 32, 0, st>>>(S, io, stats);
+  return cudaGetLastError();
+}
+
 }  // namespace qb

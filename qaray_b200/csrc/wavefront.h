@@ -236,6 +236,11 @@ void launch_trace_closest_rays(const DScene &S, const qgRay *rays, size_t n, qgH
                                cudaStream_t st);
 void launch_trace_any_rays(const DScene &S, const float *rays6, const float *tmax, size_t n, uint8_t *occ, unsigned long long *stats,
                            void *scratch, cudaStream_t st);
+// the any-hit batch with its scratch in a static device array (no allocation; qg_trace_any_noalloc): n <= QB_NOALLOC_MAX_RAYS
+#define QB_NOALLOC_MAX_RAYS (1 << 20)
+#define QB_NOALLOC_MAX_DEVICES 64
+cudaError_t launch_trace_any_rays_noalloc(const DScene &S, const float *rays6, const float *tmax, size_t n, uint8_t *occ,
+                                          unsigned long long *stats, cudaStream_t st);
 void launch_primary_rays(const WfParams &P, size_t n, qgRay *out, cudaStream_t st);
 int wf_trace_grid();   // persistent grid sizes (blocks), from the occupancy calculator
 int wf_shadow_grid();
