@@ -35,10 +35,10 @@ __device__ __forceinline__ V3 xyz(float4 v) { return v3(v.x, v.y, v.z); }
 // four 128-bit ones — every lane reads a different record, so each load instruction costs one L1 tag look-up per lane and the
 // wide form halves them. QB_GEOM_EVICT_LAST: the records additionally stay in L2 ahead of the streaming wave state.
 #ifndef QB_LD256
-#define QB_LD256 0
+#define QB_LD256 1
 #endif
 #ifndef QB_GEOM_EVICT_LAST
-#define QB_GEOM_EVICT_LAST 0
+#define QB_GEOM_EVICT_LAST 1
 #endif
 __device__ __forceinline__ void ld_rec64(const void *p, float4 &a, float4 &b, float4 &c, float4 &d)
 {
