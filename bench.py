@@ -437,8 +437,10 @@ def finish_b200(args, L):
             peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (of measured)"
         else:
             peak, peak_src = 6650.0, "B200_PROFILING.md fallback (of fallback)"
-        # launches per wave = 1 (stats) + (bounce + 1) x (trace + 2 cull-check kernels + finish + shade [+ shadow + its exact walk]); waves per step follow
-        per_wave = 1 + (BOUNCE + 1) * (5 + (2 if t["shadow"] > 0 else 0))
+        # launches per wave = 1 (stats) + (bounce + 1) x (trace + 2 cull-check kernels + shade [+ finish when the material sort
+        # keeps it a separate pass] [+ shadow + its exact walk]); waves per step follow
+        # (finish runs at depth 0 only: deeper depths use the fused shade kernel; with the material sort every depth has it, plus 3 sort kernels)
+        per_wave = 1 + (BOUNCE + 1) * (4 + (2 if t["shadow"] > 0 else 0)) + (4 * (BOUNCE + 1) if args.sort_materials else 1)
         n_waves = max(1, int(round(t["launches"] / float(args.steps) / per_wave)))
         achieved = kbytes / (kms * 1e-3) * 1e-9 if kms > 0 else 0.0
         traffic = None

@@ -577,6 +577,11 @@ int make_params(const qgScene *sc, const qgRenderParams *rp, WfParams *P, Shard 
   if (rp->material_class < QG_CLASS_PHOTONMAP || rp->material_class > QG_CLASS_PHONG_BASIC) return fail(QG_EINVAL, "unknown material_class");
   P->mtl_class = rp->material_class;
   P->carry_diff = class_carries_diff(rp->material_class) ? 1 : 0;
+  // MtlBlinn_PhotonMap in queue order: the shade kernel computes the hit attributes itself (no k_wf_finish pass, no h0..h3
+  // round trip). The material sort needs mtlID before shade and the other classes read h0..h4 in their own kernels: those
+  // keep the separate pass. QB_FUSED_FINISH=0 restores it everywhere (A/B).
+  P->fused_finish = rp->material_class == QG_CLASS_PHOTONMAP && !rp->sort_by_material ? 1 : 0;
+  if (const char *e = getenv("QB_FUSED_FINISH")) P->fused_finish = P->fused_finish && atoi(e) != 0;
   // the constructors of MtlBlinn_Basic / MtlPhong_Basic switch the lights' inverse-square falloff off for the whole
   // process (MtlBlinn_Basic.cpp:18, lights.cpp:18-30); it happens as soon as the scene file declares one material
   if (rp->use_photon_map) {
@@ -667,6 +672,9 @@ struct KernelClock {
 // ends in a latency-bound tail (its longest rays), and the other kernel's blocks fill the SMs that tail leaves idle.
 // trace(d + 1) is launched first so that it owns the SMs and shadow(d) fills in; shade(d + 1) rewrites the shadow queue
 // and therefore waits for shadow(d). (Running the main chain on a higher-priority stream changed nothing: measured.)
+#ifndef QB_FUSED_DEPTHS_DEFAULT
+#define QB_FUSED_DEPTHS_DEFAULT 0xFFFFFFFEu
+#endif
 void run_wave(qgScene *sc, WfParams P, cudaStream_t st, uint64_t *launches, KernelClock *clk = nullptr)
 {
   const WfBuffers &B = sc->wf;
@@ -676,8 +684,14 @@ void run_wave(qgScene *sc, WfParams P, cudaStream_t st, uint64_t *launches, Kern
   if (clk) clk->stamp(3, st);
   const int gt = wf_trace_grid(), gs = wf_shade_grid(), gsh = wf_shadow_grid();
   const bool any_shadow = sc->dev.num_nonambient > 0 || sc->dev_num_area > 0;
+  // which depths run the fused shade kernel (bit d; QB_FUSED_DEPTHS overrides for A/B). Depth 0 keeps the separate pass: its
+  // attributes include the two differential rays (three chain transforms, texture footprints) and run better at k_wf_finish's
+  // 8 blocks / SM. Measured, ms per step, none / d0 only / d>=1 / all: tower 71.88 / 71.92 / 71.48 / 71.57, xmas 426.4 / 431.0 / 425.8 / 430.3
+  static const unsigned fused_depths = getenv("QB_FUSED_DEPTHS") ? (unsigned) strtoul(getenv("QB_FUSED_DEPTHS"), nullptr, 0) : QB_FUSED_DEPTHS_DEFAULT;
+  const bool fused_ok = P.fused_finish != 0;
   auto shade = [&](int d) {
     P.depth = d;
+    P.fused_finish = fused_ok && ((fused_depths >> d) & 1u) ? 1 : 0;
     if (P.sort_mat) {
       launch_mat_sort(sc->dev, B, P, st);
       *launches += 3;
@@ -693,9 +707,10 @@ void run_wave(qgScene *sc, WfParams P, cudaStream_t st, uint64_t *launches, Kern
   };
   auto trace = [&](int d) {
     P.depth = d;
+    P.fused_finish = fused_ok && ((fused_depths >> d) & 1u) ? 1 : 0;
     launch_wf_trace(sc->dev, B, P, gt, st);
     if (clk) clk->stamp(0, st);
-    *launches += 4;  // traversal, the two cull-check kernels, hit attributes
+    *launches += P.fused_finish ? 3 : 4;  // traversal, the two cull-check kernels, hit attributes (unless the shade kernel computes them)
   };
   trace(0);
   shade(0);

@@ -18,6 +18,7 @@
 #include <algorithm>
 #include "wavefront.h"
 #include "trace.cuh"  // Ray3
+#include "wave_rays.cuh"  // primary_ray, HitRec, finish_hit (the fused kernel computes the hit attributes itself)
 
 namespace qb {
 
@@ -246,7 +247,17 @@ __device__ __forceinline__ void res_flush(const WfBuffers &B, int d, int lane, c
   }
 }
 
-__global__ void __launch_bounds__(QB_BLOCK) k_wf_shade(const DScene S, const WfBuffers B, const WfParams P)
+// FUSED: the hit attributes (k_wf_finish's h0..h3: 64 bytes written and read back per ray, plus a second read of the ray)
+// never leave registers — the kernel reads trace's compact record (32 bytes) and runs finish_hit itself. The attribute
+// arithmetic is the same code compiled the same way (this translation unit is built with --fmad=false like the traversal's),
+// so p, N, uvw and duvw come out bit-equal to the separate pass.
+// Residency: 5 blocks / SM (96 registers, 80 B of spills) for the fused kernel, 4 for the plain one — A/B on the tower, fused:
+// 4 / 5 / 6 blocks = 13.68 / 13.36 / 13.43 ms of shade time per step
+#ifndef QB_SHADE_FUSED_BLOCKS
+#define QB_SHADE_FUSED_BLOCKS 5
+#endif
+template <bool FUSED>
+__global__ void __launch_bounds__(QB_BLOCK, FUSED ? QB_SHADE_FUSED_BLOCKS : 4) k_wf_shade(const DScene S, const WfBuffers B, const WfParams P)
 {
   const int d = P.depth;
   const uint32_t n = d == 0 ? P.n_paths : min(B.counters[QB_CNT_PATHS + d], B.capacity);
@@ -285,10 +296,20 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade(const DScene S, const WfB
     if (idx < n) {
       // every record of the path is requested up front: the three dependent round trips (h0 -> path state -> h1..h3) were
       // the kernel's top stalls once the queue atomics were gone (profiles/README.md)
-      const float4 h0 = B.h0[idx];
-      const float4 h1 = B.h1[idx], h2 = B.h2[idx], h3 = B.h3[idx];
+      float4 h0 = make_float4(0.f, 0.f, 0.f, 0.f), h1 = B.h1[idx], h2 = B.h2[idx], h3 = h0;
+      if (!FUSED) { h0 = B.h0[idx]; h3 = B.h3[idx]; }
       float4 sa = make_float4(0.f, 0.f, 0.f, 0.f), sb = sa, sc4 = sa, se = sa;
       if (d > 0) { sa = B.ps0[pb][idx]; sb = B.ps1[pb][idx]; sc4 = B.ps2[pb][idx]; se = B.ps3[pb][idx]; }
+      HitRec rec;
+      int pi = 0, pj = 0, ps = 0;
+      if (FUSED) {
+        // h1 / h2 still hold trace's record (trace_kernels.cu put_rec); a padding lane of depth 0 has none (node is only
+        // looked at for valid paths, the object index is range-checked for the rest)
+        rec = unpack_rec(h1, h2);
+        const bool hit = rec.k >= 0 && rec.k < S.num_obj;
+        h0.x = hit ? rec.z : QB_BIGFLOAT;
+        h0.y = __int_as_float(hit ? __ldg(&S.obj_node[rec.k]) : -1);
+      }
       const int node = __float_as_int(h0.y);
       V3 ray_dir;
       V3 absorb_prev = v3(0.f);
@@ -297,6 +318,7 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade(const DScene S, const WfB
       if (d == 0) {
         int i, j, s;
         valid = wf_decode(P, idx, i, j, s, slot);
+        pi = i; pj = j; ps = s;
         if (valid) {
           rng.key = rng_key((uint32_t) (j * P.width + i), (uint32_t) s, P.seed);
           rng.n = wf_dof_draws(P);
@@ -325,6 +347,24 @@ __global__ void __launch_bounds__(QB_BLOCK) k_wf_shade(const DScene S, const WfB
         if (node < 0 && valid) accum_add(P.accum, slot, T * sample_environment(S, ray_dir));  // ComputeSecondaryRay miss (:250)
       }
       if (valid && node >= 0) {
+        if (FUSED) {  // k_wf_finish's body (trace_kernels.cu): the ray again, then the attributes of the recorded hit
+          Ray3 c, x, y;
+          if (d == 0) {
+            primary_ray(P, pi, pj, ps, c, x, y);
+          } else {
+            c.p = v3(sa.x, sa.y, sa.z);
+            c.d = v3(sa.w, sb.x, sb.y);
+            x = c;
+            y = c;
+          }
+          HitAttr h;
+          finish_hit(S, rec, c, x, y, d == 0, P.stale_tex != 0, h, nullptr);
+          h0.z = __int_as_float(h.mtl_id);
+          h0.w = __int_as_float((h.front ? 1 : 0) | (h.has_texture ? 2 : 0));
+          h1 = make_float4(h.p.x, h.p.y, h.p.z, h.N.x);
+          h2 = make_float4(h.N.y, h.N.z, h.uvw.x, h.uvw.y);
+          h3 = make_float4(h.duvw0.x, h.duvw0.y, h.duvw1.x, h.duvw1.y);
+        }
         const float z = h0.x;
         const int mtl_id = __float_as_int(h0.z);
         const int hflags = __float_as_int(h0.w);
@@ -707,19 +747,20 @@ void launch_wf_stats(const WfBuffers &B, int max_bounce, cudaStream_t st) { k_wf
 // persistent grid of one shade kernel: every SM filled to that kernel's own residency (the classes differ a lot in
 // registers, so one grid for all would hold the default class at the heaviest class's 3 blocks / SM)
 #define QB_SHADE_MAX_BLOCKS 4
-int wf_shade_grid_max() { return qb_sms() * QB_SHADE_MAX_BLOCKS; }
-static int persistent_grid_shade(const void *kernel)
+int wf_shade_grid_max() { return qb_sms() * std::max(QB_SHADE_MAX_BLOCKS, QB_SHADE_FUSED_BLOCKS); }
+static int persistent_grid_shade(const void *kernel, int max_blocks = QB_SHADE_MAX_BLOCKS)
 {
   int dev = 0, sms = 0, per_sm = 0;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, QB_BLOCK, 0);
   if (per_sm < 1) per_sm = 1;
-  if (per_sm > QB_SHADE_MAX_BLOCKS) per_sm = QB_SHADE_MAX_BLOCKS;  // measured: 4 blocks / SM is the knee (xmas shade 104.7 / 92.9 / 93.5 ms at 3 / 4 / 5, tower 11.3 / 10.8 / 13.1)
+  if (per_sm > max_blocks) per_sm = max_blocks;  // measured: 4 blocks / SM is the knee of the plain kernels (xmas shade 104.7 / 92.9 / 93.5 ms at 3 / 4 / 5, tower 11.3 / 10.8 / 13.1)
   if (const char *e = getenv("QB_SHADE_BLOCKS")) per_sm = std::max(1, std::min(per_sm, atoi(e)));  // A/B override
   return sms * per_sm;
 }
-int wf_shade_grid() { static int g = persistent_grid_shade((const void *) k_wf_shade); return g; }
+int wf_shade_grid() { static int g = persistent_grid_shade((const void *) k_wf_shade<false>); return g; }
+static int wf_shade_grid_fused() { static int g = persistent_grid_shade((const void *) k_wf_shade<true>, QB_SHADE_FUSED_BLOCKS); return g; }
 template <int C, bool PRIMARY> static int alt_grid()
 {
   static int g = persistent_grid_shade((const void *) k_wf_shade_alt<C, PRIMARY>);
@@ -734,7 +775,10 @@ void launch_wf_shade(const DScene &S, const WfBuffers &B, const WfParams &P, int
     case QG_CLASS_MONTECARLOGI: ALT(QG_CLASS_MONTECARLOGI); break;
     case QG_CLASS_BLINN_BASIC: ALT(QG_CLASS_BLINN_BASIC); break;
     case QG_CLASS_PHONG_BASIC: ALT(QG_CLASS_PHONG_BASIC); break;
-    default: k_wf_shade<<<grid, QB_BLOCK, 0, st>>>(S, B, P); break;
+    default:
+      if (P.fused_finish) k_wf_shade<true><<<wf_shade_grid_fused(), QB_BLOCK, 0, st>>>(S, B, P);
+      else k_wf_shade<false><<<grid, QB_BLOCK, 0, st>>>(S, B, P);
+      break;
   }
 }
 void launch_resolve(const float *accum, const float *depth_in, int n, int spp, int srgb, float *rgb_mean, uint8_t *rgb8, float *depth_out,

@@ -12,6 +12,7 @@
 #include "blockpool.cuh"
 #include "anyexact.cuh"
 #include "wavefront.h"
+#include "wave_rays.cuh"
 #include <algorithm>
 #include <map>
 #include <mutex>
@@ -47,23 +48,6 @@ namespace qb {
   traverse_pool<ANYHIT>(S, io, s_dyn, s_tab, cnt)
 #endif
 
-__device__ __forceinline__ float4 f4(float x, float y, float z, float w) { return make_float4(x, y, z, w); }
-
-// primary DiffRay of pixel (i,j), sample s: texpos = (i + H11(s), j + H13(s)), origin = wf_campos (lens sample with DOF)
-__device__ __forceinline__ void primary_ray(const WfParams &P, int i, int j, int s, Ray3 &c, Ray3 &x, Ray3 &y)
-{
-  const float tx = halton(s, 11) + (float) i;
-  const float ty = halton(s, 13) + (float) j;
-  const V3 cpt = P.scr_a + tx * P.scr_u + ty * P.scr_v;
-  const V3 xpt = P.scr_a + (tx + 0.01f) * P.scr_u + ty * P.scr_v;
-  const V3 ypt = P.scr_a + tx * P.scr_u + (ty + 0.01f) * P.scr_v;
-  const V3 campos = wf_campos(P, i, j, s);
-  c.p = x.p = y.p = campos;
-  c.d = normalize(cpt - campos);
-  x.d = normalize(xpt - campos);
-  y.d = normalize(ypt - campos);
-}
-
 // counting build only: stats[2..4] = BVH nodes / triangles / objects visited by closest-hit rays, [5..7] by any-hit rays
 __device__ __forceinline__ void flush_counters(unsigned long long *stats, const TraceCounters &cnt, int base = 2)
 {
@@ -96,7 +80,7 @@ __device__ __forceinline__ void st_stream(float4 *p, const float4 v)
   *p = v;
 #endif
 }
-// compact hit record of the wavefront: r0 = z, k, slot, tex_slot ; r1 = tex_t, tex_k, last_tri, -
+// compact hit record of the wavefront (wave_rays.cuh): r0 = z, k, slot, tex_slot ; r1 = tex_t, tex_k, last_tri, -
 __device__ __forceinline__ void put_rec(float4 *r0, float4 *r1, uint32_t idx, const HitRec &h)
 {
   st_stream(&r0[idx], f4(h.z, __int_as_float(h.k), __int_as_float(h.slot), __int_as_float(h.tex_slot)));
@@ -109,15 +93,6 @@ __device__ __forceinline__ void put_rec_keep_w(float4 *r0, float4 *r1, uint32_t 
   float *p = (float *) &r1[idx];
   p[0] = h.tex_t; p[1] = __int_as_float(h.tex_k); p[2] = __int_as_float(h.last_tri);
 }
-__device__ __forceinline__ HitRec get_rec(const float4 *r0, const float4 *r1, uint32_t idx)
-{
-  const float4 a = r0[idx], b = r1[idx];
-  HitRec h;
-  h.z = a.x; h.k = __float_as_int(a.y); h.slot = __float_as_int(a.z); h.tex_slot = __float_as_int(a.w);
-  h.tex_t = b.x; h.tex_k = __float_as_int(b.y); h.last_tri = __float_as_int(b.z);
-  return h;
-}
-
 struct RedoQueue {
   uint4 *q;          // {ray index, object, z at mesh entry (bits), flag}
   uint32_t cap;
@@ -692,12 +667,12 @@ void launch_wf_trace(const DScene &S, const WfBuffers &B, const WfParams &P, int
     QB_LAUNCH_TRACE(k_wf_trace<true>, grid, st, S, B, P);
     k_redo_detect<true><<<qb_sms() * 8, QB_BLOCK, 0, st>>>(S, B, P);
     QB_LAUNCH_TRACE(k_redo_exact<true>, redo_grid, st, S, B, P);
-    k_wf_finish<true><<<fg, QB_BLOCK, 0, st>>>(S, B, P);
+    if (!P.fused_finish) k_wf_finish<true><<<fg, QB_BLOCK, 0, st>>>(S, B, P);
   } else {
     QB_LAUNCH_TRACE(k_wf_trace<false>, grid, st, S, B, P);
     k_redo_detect<false><<<qb_sms() * 8, QB_BLOCK, 0, st>>>(S, B, P);
     QB_LAUNCH_TRACE(k_redo_exact<false>, redo_grid, st, S, B, P);
-    k_wf_finish<false><<<fg, QB_BLOCK, 0, st>>>(S, B, P);
+    if (!P.fused_finish) k_wf_finish<false><<<fg, QB_BLOCK, 0, st>>>(S, B, P);
   }
 }
 void launch_wf_shadow(const DScene &S, const WfBuffers &B, const WfParams &P, int grid, cudaStream_t st)

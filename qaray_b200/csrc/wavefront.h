@@ -150,6 +150,7 @@ struct WfParams {
   int32_t mtl_class;         // QG_CLASS_*: which of the reference's MtlBlinn classes shades (materials.h:57-61)
   int32_t carry_diff;        // secondary paths carry differential rays (ps4..ps6 / h4 allocated)
   int32_t no_falloff;        // DisableInverseSquareFalloff() was called (MtlBlinn_Basic.cpp:18, lights.cpp:21-30)
+  int32_t fused_finish;      // 1: no k_wf_finish launch, k_wf_shade<true> computes the hit attributes from trace's record itself
   int32_t use_photon_map;    // Scene::usePhotonMap: diffuse hits gather from pm[0] (photon map) / pm[1] (caustics map)
   DPhotonMap pm[2];
   float *accum;              // float4 per slot: sum r,g,b, weight
