@@ -396,6 +396,20 @@ int upload_scene(qgScene *sc)
   D.num_nodes = nn; D.num_obj = sc->num_obj; D.num_meshes = (int) meshes.size(); D.num_materials = (int) mats.size();
   D.num_lights = (int) lights.size(); D.num_textures = (int) texs.size(); D.num_nonambient = nonambient;
   D.bvh_stack = std::max(1, sc->max_bvh_depth + 1);
+  // ancestor-ray cache of the traversal (traverse.cuh, QB_ANC_CACHE): worth its 7 stack entries per lane when consecutive
+  // objects share their first-level group node and the larger stacks keep the same number of blocks resident
+  {
+    int shared = 0;
+    for (int k = 1; k < sc->num_obj; ++k) {
+      const int a0 = chain_off[k - 1], a1 = chain_off[k], b1 = chain_off[k + 1];
+      if (a1 - a0 >= 2 && b1 - a1 >= 2 && chain[a0] == chain[a1]) ++shared;
+    }
+    if (const char *e = getenv("QB_ANC_CACHE_OFF")) shared = atoi(e) ? 0 : shared;  // A/B
+    if (shared > 0 && trace_stack_fits(D.bvh_stack, QB_ANC_WORDS)) {
+      D.anc_cache = 1;
+      D.bvh_stack += QB_ANC_WORDS;
+    }
+  }
   sc->dev_num_area = 0;
   for (const qgLight &l : F.lights)
     if ((l.type == QG_LIGHT_POINT || l.type == QG_LIGHT_SPOT) && l.size > 0.01f) sc->dev_num_area++;

@@ -7,6 +7,7 @@
 //                per-triangle constants of IntersectTriangle (1/area, dropped axis) + the face word
 //   tri_face[]   global face id of each triangle slot; face_*[] per-face shading attributes (read once per hit)
 #pragma once
+#define QB_ANC_WORDS 7  // stack entries per lane the ancestor-ray cache of the traversal takes (traverse.cuh, QB_ANC_CACHE)
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -107,7 +108,9 @@ struct DScene {
   const uchar4 *texels;
   int32_t num_nodes, num_obj, num_meshes, num_materials, num_lights, num_textures;
   int32_t num_nonambient;
-  int32_t bvh_stack;  // deferred far children a ray can hold at once = deepest mesh BVH of the scene + 1 (sizes the pool's stacks)
+  int32_t bvh_stack;  // deferred far children a ray can hold at once = deepest mesh BVH of the scene + 1 (sizes the pool's stacks),
+                      // plus QB_ANC_WORDS entries when anc_cache is set
+  int32_t anc_cache;  // 1: the top QB_ANC_WORDS stack entries of a lane cache its ray in a shared ancestor's space (traverse.cuh)
   DTexColor background, environment;
 };
 

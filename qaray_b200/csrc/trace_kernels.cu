@@ -641,6 +641,11 @@ static int trace_grid_for(size_t rays)
   const size_t cap = (size_t) qb_sms() * 8;
   return (int) std::max<size_t>(1, std::min(g, cap));
 }
+// does a stack of `entries + extra` entries keep as many blocks of the closest-hit kernel resident as one of `entries`?
+bool trace_stack_fits(int entries, int extra)
+{
+  return trace_blocks_per_sm(k_wf_trace<false>, lanepool_smem_bytes(entries + extra)) == trace_blocks_per_sm(k_wf_trace<false>, lanepool_smem_bytes(entries));
+}
 int wf_trace_grid() { return 0; }   // persistent grids are sized at launch: they depend on the scene's stack depth
 int wf_shadow_grid() { return 0; }
 // grid <= 0: persistent grid = SMs x resident blocks

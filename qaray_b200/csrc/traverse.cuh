@@ -187,6 +187,17 @@ __device__ __forceinline__ float behind_bound(const ObjRec &o, const Ray3 &r, co
 //   bool load(uint32_t idx, Ray3 &c, float &tmax)    world-space ray; false = padding entry (skipped, store not called)
 //   void store(uint32_t idx, const HitRec &)     closest
 //   void store_any(uint32_t idx, bool occluded)  any-hit
+// QB_ANC_CACHE: objects are visited in scene-tree order, so the children of one group node follow each other (tower: three
+// planes under one node, xmas: seven planes under one and seven meshes under another). The ray in the group's space is the
+// same value for all of them — ToNodeCoords of the same ray through the same node — so it is kept and reused instead of
+// recomputed per child: 9 -> 7 node transforms per ray on the tower, 29 -> 17 on xmas, bit for bit the same rays.
+// The 7 words per lane (node id + ray) sit in QB_ANC_WORDS extra stack entries above the deepest entry a walk can reach
+// (the host adds them to DScene::bvh_stack and sets DScene::anc_cache) — but only where they do not cost a resident block:
+// on the tower the deeper stacks leave no room at 8 blocks / SM and the cache would lose more (75.3 ms per step at 7 blocks
+// against 71.5) than it saves; on xmas it fits: 425.4 -> 415.2 ms.
+#ifndef QB_ANC_CACHE
+#define QB_ANC_CACHE 1
+#endif
 // Words of a lane's COLD state, kept in shared memory ([word][thread], thread-private: no synchronisation, no bank
 // conflicts): what only the NEXT phase (a few times per ray) or a rare branch touches. With these 17 values in registers
 // the closest-hit kernels needed 80 registers (6 blocks / SM); without them they fit 64 and run 8 blocks / SM — a third
@@ -475,6 +486,22 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
           Ray3 c0;
           c0.p = v3(CWF(CW_C0PX), CWF(CW_C0PY), CWF(CW_C0PZ));
           c0.d = v3(CWF(CW_C0DX), CWF(CW_C0DY), CWF(CW_C0DZ));
+#if QB_ANC_CACHE
+          if (S.anc_cache && k < QB_TAB_OBJS && T.chain_ok && o.id.w - o.id.z >= 2) {
+            const int anc = T.chain[o.id.z];
+            uint32_t *aw = stk + (S.bvh_stack - QB_ANC_WORDS) * QB_BLOCK;  // word w of this lane at aw[w * QB_BLOCK]
+            if ((int) aw[0] == anc) {
+              r.p = v3(__uint_as_float(aw[1 * QB_BLOCK]), __uint_as_float(aw[2 * QB_BLOCK]), __uint_as_float(aw[3 * QB_BLOCK]));
+              r.d = v3(__uint_as_float(aw[4 * QB_BLOCK]), __uint_as_float(aw[5 * QB_BLOCK]), __uint_as_float(aw[6 * QB_BLOCK]));
+            } else {
+              r = to_node_tab(S, T, anc, c0);
+              aw[0] = (uint32_t) anc;
+              aw[1 * QB_BLOCK] = __float_as_uint(r.p.x); aw[2 * QB_BLOCK] = __float_as_uint(r.p.y); aw[3 * QB_BLOCK] = __float_as_uint(r.p.z);
+              aw[4 * QB_BLOCK] = __float_as_uint(r.d.x); aw[5 * QB_BLOCK] = __float_as_uint(r.d.y); aw[6 * QB_BLOCK] = __float_as_uint(r.d.z);
+            }
+            for (int c = o.id.z + 1; c < o.id.w; ++c) r = to_node_tab(S, T, T.chain[c], r);
+          } else
+#endif
           r = chain_ray_tab(S, T, o, k, c0);
           const int type = o.id.x;
           QB_CNT(objects);
@@ -529,6 +556,9 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
             CW(CW_HTEXT) = 0u; CW(CW_HLASTTRI) = 0xFFFFFFFFu;
           }
           CW(CW_UVSLOT) = 0xFFFFFFFFu;
+#if QB_ANC_CACHE
+          if (S.anc_cache) stk[(S.bvh_stack - QB_ANC_WORDS) * QB_BLOCK] = 0xFFFFFFFFu;
+#endif
           k = 0; sp = 0; cur = QB_REF_EMPTY; obj_slot = -1;
           active = true;
         }

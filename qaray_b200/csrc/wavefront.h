@@ -243,6 +243,7 @@ void launch_trace_any_rays(const DScene &S, const float *rays6, const float *tma
 cudaError_t launch_trace_any_rays_noalloc(const DScene &S, const float *rays6, const float *tmax, size_t n, uint8_t *occ,
                                           unsigned long long *stats, cudaStream_t st);
 void launch_primary_rays(const WfParams &P, size_t n, qgRay *out, cudaStream_t st);
+bool trace_stack_fits(int entries, int extra);  // `extra` more stack entries per lane cost no resident block of the traversal kernels
 int wf_trace_grid();   // persistent grid sizes (blocks), from the occupancy calculator
 int wf_shadow_grid();
 int wf_shade_grid();
