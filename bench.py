@@ -500,6 +500,12 @@ def finish_b200(args, L):
 
 def main():
     args = parse_args()
+    # stdout carries the ONE JSON line and nothing else: libraries that print there (NCCL's version banner ignores
+    # NCCL_DEBUG_FILE) are pointed at stderr at the descriptor level, and Python's stdout keeps the original descriptor
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real_stdout, "w", buffering=1)
     if args.impl == "reference":
         return run_reference_arm(args)
     return run_b200_arm(args)
