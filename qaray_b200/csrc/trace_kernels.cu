@@ -628,7 +628,14 @@ template <class K> static int trace_blocks_per_sm(K kernel, size_t smem)
   const auto key = std::make_tuple((const void *) kernel, smem, dev);
   auto it = cache.find(key);
   if (it != cache.end()) return it->second;
-  if (smem > 48 * 1024) cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+  // the opt-in above 48 KB is one value per (kernel, device): only ever raised, so that a shallower scene's query does not
+  // take away what a deeper scene's later launches (answered from the cache above) still need
+  static std::map<std::pair<const void *, int>, size_t> opted;
+  size_t &have = opted[std::make_pair((const void *) kernel, dev)];
+  if (smem > 48 * 1024 && smem > have) {
+    cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+    have = smem;
+  }
   int per_sm = 0;
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, QB_BLOCK, smem);
   if (per_sm < 1) per_sm = 1;
