@@ -23,11 +23,14 @@ namespace qb {
 #ifndef QB_W_LEAF
 #define QB_W_LEAF 8
 #endif
+// vote weights (INNER counts 4 per lane). Re-tuned on the final kernels, ms per step tower / xmas: NEXT 6 + FETCH 4 (before)
+// 71.8 / 419.4; FETCH 2: 71.2 / 404.6; NEXT 4: 71.5 / 414.6; FETCH 2 + NEXT 5: 71.3 / 402.8; + NEXT 4: 71.85 / 401.0; + NEXT 3:
+// 71.7 / 398.9; FETCH 1: 72.7; LEAF 6 / 10 / 12: 72.7 / 71.75 / 71.8
 #ifndef QB_W_NEXT
-#define QB_W_NEXT 6
+#define QB_W_NEXT 5
 #endif
 #ifndef QB_W_FETCH
-#define QB_W_FETCH 4
+#define QB_W_FETCH 2
 #endif
 #define QB_COOP_SLOTS 128          // (ray, triangle) pairs a warp's LEAF phase handles per round
 #define QB_REF_EMPTY 0x7FFFFFFFu   // "no current node" (an internal index never reaches 2^31-1)
