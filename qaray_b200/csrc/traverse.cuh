@@ -32,6 +32,15 @@ namespace qb {
 #ifndef QB_W_FETCH
 #define QB_W_FETCH 2
 #endif
+#ifndef QB_W_LEAF_ANY  // the any-hit kernels' own weights
+#define QB_W_LEAF_ANY QB_W_LEAF
+#endif
+#ifndef QB_W_NEXT_ANY
+#define QB_W_NEXT_ANY QB_W_NEXT
+#endif
+#ifndef QB_W_FETCH_ANY
+#define QB_W_FETCH_ANY QB_W_FETCH
+#endif
 #define QB_COOP_SLOTS 128          // (ray, triangle) pairs a warp's LEAF phase handles per round
 #define QB_REF_EMPTY 0x7FFFFFFFu   // "no current node" (an internal index never reaches 2^31-1)
 #ifndef QB_NEXT_REPS
@@ -256,7 +265,8 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
     const int n_fetch = __popc(m_fetch), n_inner = __popc(m_inner), n_leaf = __popc(m_leaf), n_next = __popc(m_next);
 
     // weighted plurality (weights in quarters): the cheap phases may be given more than their head count
-    const int w_inner = 4 * n_inner, w_leaf = QB_W_LEAF * n_leaf, w_next = QB_W_NEXT * n_next, w_fetch = QB_W_FETCH * n_fetch;
+    const int w_inner = 4 * n_inner, w_leaf = (ANY ? QB_W_LEAF_ANY : QB_W_LEAF) * n_leaf, w_next = (ANY ? QB_W_NEXT_ANY : QB_W_NEXT) * n_next,
+              w_fetch = (ANY ? QB_W_FETCH_ANY : QB_W_FETCH) * n_fetch;
     if (w_inner >= w_leaf && w_inner >= w_next && w_inner >= w_fetch) {
       // ---- INNER: node visits (both children's boxes); the near child becomes current, the far child is deferred.
       // Up to QB_INNER_REPS visits per vote while at least half of the lanes that started are still on inner nodes.
