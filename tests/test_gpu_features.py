@@ -8,6 +8,8 @@ RMSE(gpu, a) <= 1.25 * RMSE(a, b) on clamped linear radiance, frame means within
 * adaptive  additionally the per-pixel sample counts: mean count within 10 % of the reference's, count planes as close
             to reference run A as reference run B is (x1.5), and the sample-count plane = 255 * s / sppMax
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -113,3 +115,52 @@ def test_adaptive_tile_shards_union_equals_whole_frame():
         assert np.array_equal(sc[mask == 1], whole[2][mask == 1])
     assert (cover == 1).all()
     assert np.allclose(acc, whole[0], rtol=1e-5, atol=1e-6)
+
+
+FUSED_WORKER = r'''
+import os, sys
+import numpy as np
+sys.path.insert(0, %(root)r)
+sys.path.insert(0, os.path.join(%(root)r, "tests"))
+from conftest import ASSETS, scene_xml
+from qaray_b200.renderer import RendererParam, Scene
+name, out = sys.argv[1], sys.argv[2]
+sc = Scene.load(scene_xml(name), ASSETS)
+info = sc.info()
+W, H = info.camera.width, info.camera.height
+rng = np.random.default_rng(7)
+n = 20000
+pix = np.stack([rng.integers(0, W, n), rng.integers(0, H, n), rng.integers(0, 64, n)], 1).astype(np.int32)
+rgb, z = sc.sample_radiance(RendererParam(spp=64, max_bounce=5, srgb=True, seed=0x5EED), pix)
+sc.close()
+np.savez(out, rgb=rgb, z=z)
+'''
+
+
+@pytest.mark.parametrize("name", ["trc_scene_tower", "trc_scene_xmas", "example_project7_object"])
+def test_fused_shade_gives_the_same_samples_as_the_separate_attribute_pass(name, tmp_path):
+    """k_wf_shade<true> computes the hit attributes itself at depths >= 1 (DESIGN.md 4); QB_FUSED_FINISH=0 brings the separate
+    k_wf_finish pass back for every depth. Single samples (one accumulation slot each, so no atomic order is involved) must come
+    out the same: position, normal, texture coordinates and footprints are the same arithmetic either way. Distances bit for bit;
+    radiance up to the order in which the shadow kernel's lanes add the lights of one hit into the sample's slot (fp32 atomics:
+    an ulp or two when two or more lights are visible), which differs from run to run in either mode."""
+    import subprocess
+    import sys
+    from conftest import ROOT
+    res = []
+    for fused in ("1", "0"):
+        out = str(tmp_path / ("fused%s.npz" % fused))
+        env = dict(os.environ, QB_FUSED_FINISH=fused)
+        r = subprocess.run([sys.executable, "-c", FUSED_WORKER % {"root": ROOT}, name, out], env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE,
+                           text=True, timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        res.append(np.load(out))
+    a, b = res
+    assert np.isfinite(a["rgb"]).mean() > 0.99 and a["rgb"].sum() > 0
+    assert np.array_equal(a["z"].view(np.uint32), b["z"].view(np.uint32))
+    fin = np.isfinite(a["rgb"]).all(axis=1)
+    assert np.array_equal(fin, np.isfinite(b["rgb"]).all(axis=1))
+    same = (a["rgb"].view(np.uint32) == b["rgb"].view(np.uint32)).all(axis=1)
+    assert same.mean() >= 0.9, "only %.1f %% of the samples are bit-equal" % (100 * same.mean())
+    close = np.abs(a["rgb"][fin] - b["rgb"][fin]) <= 1e-7 + 4e-6 * np.abs(b["rgb"][fin])
+    assert close.all(), "%d samples differ between the fused and the separate pass beyond the order of additions" % (~close.all(axis=1)).sum()
