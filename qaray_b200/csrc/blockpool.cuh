@@ -121,8 +121,9 @@ __device__ __forceinline__ int bp_phase_of(uint32_t cur) { return cur == QB_REF_
 // IO concept: as traverse.cuh (count, cursor, map, load, store, store_any, defer, exact); every call names the ray by index,
 // so an IO object must not keep per-ray state between calls (a ray is advanced by different threads over its life).
 template <bool ANY, class IO>
-__device__ __forceinline__ void traverse_block(const DScene &S, IO &io, uint32_t *sm, int entries, const SceneTab &T, TraceCounters &cnt)
+__device__ __forceinline__ void traverse_block(const DScene &S, IO &io, uint32_t *sm, int entries, const SceneTab &tab, TraceCounters &cnt)
 {
+  TabRef T = tab_ref(tab);
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const uint32_t lt_mask = (1u << lane) - 1u;
   const uint32_t FULL = 0xFFFFFFFFu;

@@ -17,6 +17,26 @@
 
 namespace qb {
 
+#ifndef QB_STACK_ASM
+#define QB_STACK_ASM 1
+#endif
+// shared memory through 32-bit shared-space addresses (see QB_STACK_ASM in traverse_pool); volatile keeps the accesses of one
+// thread in program order, which is all the thread-private words need
+__device__ __forceinline__ uint32_t smem_addr(const void *p) { return (uint32_t) __cvta_generic_to_shared(p); }
+__device__ __forceinline__ void sts_u32(uint32_t a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v)); }
+__device__ __forceinline__ uint32_t lds_u32(uint32_t a)
+{
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ float4 lds_f4(uint32_t a)
+{
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+  return v;
+}
+
 #ifndef QB_COOP_LEAF
 #define QB_COOP_LEAF 1
 #endif
@@ -134,22 +154,55 @@ __device__ __forceinline__ Ray3 to_node_q(float4 i0, float4 i1, float4 i2, Ray3 
   o.d = q - o.p;
   return o;
 }
-__device__ __forceinline__ Ray3 to_node_tab(const DScene &S, const SceneTab &T, int n, Ray3 r)
+#if QB_STACK_ASM
+// the block's table through its 32-bit shared address (TabRef = that address; see QB_STACK_ASM)
+typedef uint32_t TabRef;
+__device__ __forceinline__ TabRef tab_ref(const SceneTab &T) { return smem_addr(&T); }
+__device__ __forceinline__ int tab_chain(TabRef T, int c) { return (int) lds_u32(T + (uint32_t) offsetof(SceneTab, chain) + 4u * (uint32_t) c); }
+__device__ __forceinline__ bool tab_chain_ok(TabRef T) { return lds_u32(T + (uint32_t) offsetof(SceneTab, chain_ok)) != 0u; }
+__device__ __forceinline__ Ray3 to_node_tab(const DScene &S, TabRef T, int n, Ray3 r)
+{
+  if (n < QB_TAB_NODES) {
+    const uint32_t a = T + (uint32_t) offsetof(SceneTab, node) + 48u * (uint32_t) n;
+    return to_node_q(lds_f4(a), lds_f4(a + 16u), lds_f4(a + 32u), r);
+  }
+  return to_node(&S.nodes[n], r);
+}
+__device__ __forceinline__ ObjRec obj_rec(const DScene &S, TabRef T, int k)
+{
+  if (k < QB_TAB_OBJS) {
+    const uint32_t a = T + (uint32_t) offsetof(SceneTab, obj) + (uint32_t) sizeof(ObjRec) * (uint32_t) k;
+    ObjRec o;
+    o.lo = lds_f4(a);
+    o.hi = lds_f4(a + 16u);
+    const float4 id = lds_f4(a + 32u);
+    o.id = make_int4(__float_as_int(id.x), __float_as_int(id.y), __float_as_int(id.z), __float_as_int(id.w));
+    return o;
+  }
+  return make_obj_rec(S, k);
+}
+#else
+typedef const SceneTab &TabRef;
+__device__ __forceinline__ TabRef tab_ref(const SceneTab &T) { return T; }
+__device__ __forceinline__ int tab_chain(TabRef T, int c) { return T.chain[c]; }
+__device__ __forceinline__ bool tab_chain_ok(TabRef T) { return T.chain_ok != 0; }
+__device__ __forceinline__ Ray3 to_node_tab(const DScene &S, TabRef T, int n, Ray3 r)
 {
   if (n < QB_TAB_NODES) return to_node_q(T.node[n][0], T.node[n][1], T.node[n][2], r);
   return to_node(&S.nodes[n], r);
 }
-__device__ __forceinline__ ObjRec obj_rec(const DScene &S, const SceneTab &T, int k)
+__device__ __forceinline__ ObjRec obj_rec(const DScene &S, TabRef T, int k)
 {
   if (k < QB_TAB_OBJS) return T.obj[k];
   return make_obj_rec(S, k);
 }
+#endif
 // ray of object k's node space (the root's transform already applied to r0): chain_ray through the table
-__device__ __forceinline__ Ray3 chain_ray_tab(const DScene &S, const SceneTab &T, const ObjRec &o, int k, Ray3 r0)
+__device__ __forceinline__ Ray3 chain_ray_tab(const DScene &S, TabRef T, const ObjRec &o, int k, Ray3 r0)
 {
   Ray3 r = r0;
-  if (k < QB_TAB_OBJS && T.chain_ok) {
-    for (int c = o.id.z; c < o.id.w; ++c) r = to_node_tab(S, T, T.chain[c], r);
+  if (k < QB_TAB_OBJS && tab_chain_ok(T)) {
+    for (int c = o.id.z; c < o.id.w; ++c) r = to_node_tab(S, T, tab_chain(T, c), r);
   } else {
     for (int c = o.id.z; c < o.id.w; ++c) r = to_node_tab(S, T, __ldg(&S.chain[c]), r);
   }
@@ -225,16 +278,35 @@ enum {
 __host__ __device__ inline size_t lanepool_smem_bytes(int entries) { return 4u * ((size_t) (entries + CW_COUNT) * QB_BLOCK + (QB_BLOCK / 32) * QB_COOP_SLOTS); }
 
 template <bool ANY, class IO>
-__device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t *__restrict__ s_dyn, const SceneTab &T, TraceCounters &cnt)
+__device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t *__restrict__ s_dyn, const SceneTab &tab, TraceCounters &cnt)
 {
+  TabRef T = tab_ref(tab);
   const int lane = threadIdx.x & 31;
   const uint32_t lt_mask = (1u << lane) - 1u;
   const uint32_t n = io.count();
   uint32_t *stk = s_dyn + threadIdx.x;  // entry e at stk[e * QB_BLOCK]
+#if QB_STACK_ASM
+  // The same entries through 32-bit shared-space addresses: nvcc re-derives the shared window base for every access made
+  // through the generic pointer (S2UR SR_CgaCtaId + 3 uniform ops before each STS / LDS: ~11 issue slots per node visit for
+  // its push and pop); with the lane's base kept in one register an access is one IMAD + the STS / LDS.
+  const uint32_t stk_a = (uint32_t) __cvta_generic_to_shared(stk);
+#define STK_PUT(e, v) asm volatile("st.shared.u32 [%0], %1;" ::"r"(stk_a + (uint32_t) (e) * (QB_BLOCK * 4u)), "r"(v))
+#define STK_GET(e, v) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(stk_a + (uint32_t) (e) * (QB_BLOCK * 4u)))
+#else
+#define STK_PUT(e, v) (stk[(e) * QB_BLOCK] = (v))
+#define STK_GET(e, v) ((v) = stk[(e) * QB_BLOCK])
+#endif
   uint32_t *cold = s_dyn + S.bvh_stack * QB_BLOCK + threadIdx.x;
   uint32_t *s_coop = s_dyn + (S.bvh_stack + CW_COUNT) * QB_BLOCK;
-#define CW(f) cold[(f) * QB_BLOCK]
-#define CWF(f) __uint_as_float(cold[(f) * QB_BLOCK])
+#if QB_STACK_ASM
+  const uint32_t cold_a = smem_addr(cold);
+#define CWGET(f) lds_u32(cold_a + (uint32_t) (f) * (QB_BLOCK * 4u))
+#define CWSET(f, v) sts_u32(cold_a + (uint32_t) (f) * (QB_BLOCK * 4u), (v))
+#else
+#define CWGET(f) (cold[(f) * QB_BLOCK])
+#define CWSET(f, v) (cold[(f) * QB_BLOCK] = (v))
+#endif
+#define CWF(f) __uint_as_float(CWGET(f))
 
   bool active = false, exhausted = false;
   uint32_t idx = 0;
@@ -355,12 +427,12 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
             const bool first0 = entry0 < entry1;  // the reference pushes the other child first, then this one
             const bool take0 = both ? first0 : h0;
             const uint32_t near_ref = take0 ? ndr.x : ndr.y, far_ref = take0 ? ndr.y : ndr.x;
-            if (both) stk[sp * QB_BLOCK] = far_ref;
+            if (both) STK_PUT(sp, far_ref);
             sp += both ? 1 : 0;
             const bool pop = none && sp > 0;
             sp -= pop ? 1 : 0;
             uint32_t popped = QB_REF_EMPTY;
-            if (pop) popped = stk[sp * QB_BLOCK];
+            if (pop) STK_GET(sp, popped);
             cur = none ? popped : near_ref;
           }
         }
@@ -387,7 +459,7 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
             if (ANY) { io.store_any(idx, true); active = false; break; }
             hz = t;
             obj_slot = (int) (base + i);
-            if (__float_as_uint(td.z) & 0x80000000u) { CW(CW_UVSLOT) = (uint32_t) obj_slot; CW(CW_UVT) = __float_as_uint(t); }
+            if (__float_as_uint(td.z) & 0x80000000u) { CWSET(CW_UVSLOT, (uint32_t) obj_slot); CWSET(CW_UVT, __float_as_uint(t)); }
           }
         }
       }
@@ -405,12 +477,21 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
         const uint32_t excl = incl - count;
         const uint32_t total = min(__reduce_max_sync(0xFFFFFFFFu, count ? incl : 0u), (uint32_t) QB_COOP_SLOTS);
         uint32_t *scr = s_coop + (threadIdx.x >> 5) * QB_COOP_SLOTS;
-        for (uint32_t i = 0; i < count; ++i) scr[excl + i] = ((uint32_t) lane << 3) | i;
+#if QB_STACK_ASM
+        const uint32_t scr_a = smem_addr(scr);
+#define SCR_PUT(i, v) sts_u32(scr_a + 4u * (uint32_t) (i), (v))
+#define SCR_GET(i) lds_u32(scr_a + 4u * (uint32_t) (i))
+#else
+#define SCR_PUT(i, v) (scr[(i)] = (v))
+#define SCR_GET(i) (scr[(i)])
+#endif
+        for (uint32_t i = 0; i < count; ++i) SCR_PUT(excl + i, ((uint32_t) lane << 3) | i);
         __syncwarp();
         for (uint32_t q0 = 0; q0 < total; q0 += 32u) {
           const uint32_t q = q0 + (uint32_t) lane;
           const bool have = q < total;
-          const uint32_t code = have ? scr[q] : 0u;
+          uint32_t code = 0u;
+          if (have) code = SCR_GET(q);
           const int o = (int) (code >> 3);
           const uint32_t tb = __shfl_sync(0xFFFFFFFFu, lbase, o);
           Ray3 rr;
@@ -424,20 +505,21 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
             float t;
             const bool ok = tri_candidate(rr, xyz(ta), xyz(tb4), xyz(tc), v3(ta.w, tb4.w, tc.w), td.x, __float_as_int(td.y), t);
             // accepted candidates have t > bias > 0; bit 0 of a rejected entry's word is never looked at
-            scr[q] = ok ? __float_as_uint(t) : 0x80000000u;
+            SCR_PUT(q, ok ? __float_as_uint(t) : 0x80000000u);
           }
         }
         __syncwarp();
         if (count) {
-          cur = sp > 0 ? stk[(--sp) * QB_BLOCK] : QB_REF_EMPTY;
+          cur = QB_REF_EMPTY;
+          if (sp > 0) { --sp; STK_GET(sp, cur); }
           for (uint32_t i = 0; i < count; ++i) {
-            const uint32_t w = scr[excl + i];
+            const uint32_t w = SCR_GET(excl + i);
             const float t = __uint_as_float(w);
             if (!(w & 0x80000000u) && hz > t) {
               if (ANY) { io.store_any(idx, true); active = false; break; }
               hz = t;
               obj_slot = (int) (lbase + i);
-              if (__ldg(&S.tri_face[lbase + i]) & 0x80000000u) { CW(CW_UVSLOT) = (uint32_t) obj_slot; CW(CW_UVT) = __float_as_uint(t); }
+              if (__ldg(&S.tri_face[lbase + i]) & 0x80000000u) { CWSET(CW_UVSLOT, (uint32_t) obj_slot); CWSET(CW_UVT, __float_as_uint(t)); }
             }
           }
         }
@@ -472,16 +554,16 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
             redo = true;
             cull_state = 2;
             hz = z_entry;
-            obj_slot = -1; CW(CW_UVSLOT) = 0xFFFFFFFFu; sp = 0;
+            obj_slot = -1; CWSET(CW_UVSLOT, 0xFFFFFFFFu); sp = 0;
             cur = __float_as_uint(obj_rec(S, T, k - 1).lo.w);
           }
         }
       }
       if (go_next && !redo && !handed_over) {
         if (!ANY && k > 0 && obj_slot >= 0) {
-          CW(CW_HK) = (uint32_t) (k - 1); CW(CW_HSLOT) = (uint32_t) obj_slot; CW(CW_HLASTTRI) = (uint32_t) obj_slot;
-          const uint32_t uv_slot = CW(CW_UVSLOT);
-          if ((int) uv_slot >= 0) { CW(CW_HTEXK) = (uint32_t) (k - 1); CW(CW_HTEXSLOT) = uv_slot; CW(CW_HTEXT) = CW(CW_UVT); }
+          CWSET(CW_HK, (uint32_t) (k - 1)); CWSET(CW_HSLOT, (uint32_t) obj_slot); CWSET(CW_HLASTTRI, (uint32_t) obj_slot);
+          const uint32_t uv_slot = CWGET(CW_UVSLOT);
+          if ((int) uv_slot >= 0) { CWSET(CW_HTEXK, (uint32_t) (k - 1)); CWSET(CW_HTEXSLOT, uv_slot); CWSET(CW_HTEXT, CWGET(CW_UVT)); }
         }
         obj_slot = -1;
         if (k == S.num_obj) {
@@ -489,8 +571,8 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
             io.store_any(idx, false);
           } else {
             HitRec h;
-            h.z = hz; h.k = (int) CW(CW_HK); h.slot = (int) CW(CW_HSLOT); h.tex_k = (int) CW(CW_HTEXK); h.tex_slot = (int) CW(CW_HTEXSLOT);
-            h.tex_t = CWF(CW_HTEXT); h.last_tri = (int) CW(CW_HLASTTRI);
+            h.z = hz; h.k = (int) CWGET(CW_HK); h.slot = (int) CWGET(CW_HSLOT); h.tex_k = (int) CWGET(CW_HTEXK); h.tex_slot = (int) CWGET(CW_HTEXSLOT);
+            h.tex_t = CWF(CW_HTEXT); h.last_tri = (int) CWGET(CW_HLASTTRI);
             io.store(idx, h);
           }
           active = false;
@@ -500,8 +582,8 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
           c0.p = v3(CWF(CW_C0PX), CWF(CW_C0PY), CWF(CW_C0PZ));
           c0.d = v3(CWF(CW_C0DX), CWF(CW_C0DY), CWF(CW_C0DZ));
 #if QB_ANC_CACHE
-          if (S.anc_cache && k < QB_TAB_OBJS && T.chain_ok && o.id.w - o.id.z >= 2) {
-            const int anc = T.chain[o.id.z];
+          if (S.anc_cache && k < QB_TAB_OBJS && tab_chain_ok(T) && o.id.w - o.id.z >= 2) {
+            const int anc = tab_chain(T, o.id.z);
             uint32_t *aw = stk + (S.bvh_stack - QB_ANC_WORDS) * QB_BLOCK;  // word w of this lane at aw[w * QB_BLOCK]
             if ((int) aw[0] == anc) {
               r.p = v3(__uint_as_float(aw[1 * QB_BLOCK]), __uint_as_float(aw[2 * QB_BLOCK]), __uint_as_float(aw[3 * QB_BLOCK]));
@@ -512,23 +594,23 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
               aw[1 * QB_BLOCK] = __float_as_uint(r.p.x); aw[2 * QB_BLOCK] = __float_as_uint(r.p.y); aw[3 * QB_BLOCK] = __float_as_uint(r.p.z);
               aw[4 * QB_BLOCK] = __float_as_uint(r.d.x); aw[5 * QB_BLOCK] = __float_as_uint(r.d.y); aw[6 * QB_BLOCK] = __float_as_uint(r.d.z);
             }
-            for (int c = o.id.z + 1; c < o.id.w; ++c) r = to_node_tab(S, T, T.chain[c], r);
+            for (int c = o.id.z + 1; c < o.id.w; ++c) r = to_node_tab(S, T, tab_chain(T, c), r);
           } else
 #endif
           r = chain_ray_tab(S, T, o, k, c0);
           const int type = o.id.x;
           QB_CNT(objects);
           ++k;
-          CW(CW_UVSLOT) = 0xFFFFFFFFu;
+          CWSET(CW_UVSLOT, 0xFFFFFFFFu);
           if (type == QG_OBJ_MESH) {
             const uint32_t root_ref = __float_as_uint(o.lo.w);
             float mesh_exit;
             if (root_ref != QB_NO_FACES && mesh_box_hit_q(o, r, hz, mesh_exit, drcp) && !(mesh_exit < (bcull = behind_bound(o, r, drcp)))) {
               cur = root_ref;
               cull_state = io.exact(idx, k - 1) ? 2 : 0;  // k was advanced above: k - 1 is this object
-              CW(CW_ZENTRY) = __float_as_uint(hz);
-              CW(CW_ZSANE) = __float_as_uint(qmax(mesh_exit * 1.001f, o.hi.w));
-              CW(CW_MEXIT) = __float_as_uint(mesh_exit);
+              CWSET(CW_ZENTRY, __float_as_uint(hz));
+              CWSET(CW_ZSANE, __float_as_uint(qmax(mesh_exit * 1.001f, o.hi.w)));
+              CWSET(CW_MEXIT, __float_as_uint(mesh_exit));
               gx = qabs(r.d.x) < 1e-7f; gy = qabs(r.d.y) < 1e-7f; gz = qabs(r.d.z) < 1e-7f;
             }
           } else {
@@ -539,8 +621,8 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
                 active = false;
               } else {
                 hz = t;
-                CW(CW_HK) = (uint32_t) (k - 1); CW(CW_HSLOT) = 0xFFFFFFFFu;
-                CW(CW_HTEXK) = (uint32_t) (k - 1); CW(CW_HTEXSLOT) = 0xFFFFFFFFu; CW(CW_HTEXT) = __float_as_uint(t);  // sphere / plane always write uvw
+                CWSET(CW_HK, (uint32_t) (k - 1)); CWSET(CW_HSLOT, 0xFFFFFFFFu);
+                CWSET(CW_HTEXK, (uint32_t) (k - 1)); CWSET(CW_HTEXSLOT, 0xFFFFFFFFu); CWSET(CW_HTEXT, __float_as_uint(t));  // sphere / plane always write uvw
               }
             }
           }
@@ -561,14 +643,14 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
         if (my < n && io.load(ray, c, tmax)) {
           idx = ray;
           const Ray3 c0 = to_node_tab(S, T, 0, c);
-          CW(CW_C0PX) = __float_as_uint(c0.p.x); CW(CW_C0PY) = __float_as_uint(c0.p.y); CW(CW_C0PZ) = __float_as_uint(c0.p.z);
-          CW(CW_C0DX) = __float_as_uint(c0.d.x); CW(CW_C0DY) = __float_as_uint(c0.d.y); CW(CW_C0DZ) = __float_as_uint(c0.d.z);
+          CWSET(CW_C0PX, __float_as_uint(c0.p.x)); CWSET(CW_C0PY, __float_as_uint(c0.p.y)); CWSET(CW_C0PZ, __float_as_uint(c0.p.z));
+          CWSET(CW_C0DX, __float_as_uint(c0.d.x)); CWSET(CW_C0DY, __float_as_uint(c0.d.y)); CWSET(CW_C0DZ, __float_as_uint(c0.d.z));
           hz = tmax;
           if (!ANY) {
-            CW(CW_HK) = 0xFFFFFFFFu; CW(CW_HSLOT) = 0xFFFFFFFFu; CW(CW_HTEXK) = 0xFFFFFFFFu; CW(CW_HTEXSLOT) = 0xFFFFFFFFu;
-            CW(CW_HTEXT) = 0u; CW(CW_HLASTTRI) = 0xFFFFFFFFu;
+            CWSET(CW_HK, 0xFFFFFFFFu); CWSET(CW_HSLOT, 0xFFFFFFFFu); CWSET(CW_HTEXK, 0xFFFFFFFFu); CWSET(CW_HTEXSLOT, 0xFFFFFFFFu);
+            CWSET(CW_HTEXT, 0u); CWSET(CW_HLASTTRI, 0xFFFFFFFFu);
           }
-          CW(CW_UVSLOT) = 0xFFFFFFFFu;
+          CWSET(CW_UVSLOT, 0xFFFFFFFFu);
 #if QB_ANC_CACHE
           if (S.anc_cache) stk[(S.bvh_stack - QB_ANC_WORDS) * QB_BLOCK] = 0xFFFFFFFFu;
 #endif
@@ -578,7 +660,8 @@ __device__ __forceinline__ void traverse_pool(const DScene &S, IO &io, uint32_t 
       }
     }
   }
-#undef CW
+#undef CWGET
+#undef CWSET
 #undef CWF
 }
 
